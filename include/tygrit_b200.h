@@ -1,0 +1,168 @@
+/*
+ * tygrit_b200.h — C ABI of the B200-native collision-checking engine that sits
+ * behind TyGrit's MotionPlanner / CollisionCheckFn / Scene / robot-filter surface.
+ *
+ * There is no FFI in the reference: its planner reaches the collision arithmetic
+ * through pybind11 into third-party VAMP (TyGrit/planning/fetch/vamp_preview.py).
+ * Each entry point below names the reference call it replaces (file:line relative
+ * to the TyGrit tree).  INTEGRATION.md shows the ctypes binding a maintainer adds.
+ *
+ * Conventions
+ *  - every pointer marked DEVICE is a CUDA device pointer on the env's device
+ *    (e.g. torch.Tensor.data_ptr()); pointers marked HOST are ordinary host memory;
+ *  - the library never frees caller memory and never keeps a caller pointer after
+ *    the call has been enqueued;
+ *  - `stream` is a cudaStream_t passed as void* (0 = default stream); calls are
+ *    asynchronous unless documented otherwise;
+ *  - return value: 0 = ok, < 0 = error (TG_E_*); tg_last_error() gives the text;
+ *  - base poses are [x, y, theta] (vamp_preview.py:103-104,162), arm is the 8
+ *    planning joints [torso, shoulder_pan, ..., wrist_roll] (constants.py:54-63);
+ *  - verdict bytes: 1 = collision-free, 0 = in collision
+ *    (validate_config semantics, vamp_preview.py:159-163).
+ */
+#ifndef TYGRIT_B200_H
+#define TYGRIT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TG_OK 0
+#define TG_E_ARG (-1)      /* bad argument                                     */
+#define TG_E_CUDA (-2)     /* a CUDA runtime call failed (see tg_last_error)   */
+#define TG_E_CAPACITY (-3) /* cloud larger than the env was created for        */
+#define TG_E_STATE (-4)    /* call not valid in the env's current state        */
+
+#define TG_N_SPHERES 111 /* Fetch collision spheres (constants.py:84-225)       */
+#define TG_N_LINKS 15    /* links returned by forward_kinematics (fk_numpy.py)  */
+#define TG_MAX_OBSTACLES 64
+#define TG_MAX_ATTACHED 64
+
+typedef struct tg_env tg_env; /* opaque: device buffers of one collision world  */
+
+/* ---- library ---------------------------------------------------------------- */
+const char* tg_last_error(void);
+int tg_version(void);
+
+/* ---- environment (replaces vamp_preview.Environment, vamp_preview.py:46) ----- */
+/* max_points: capacity of the cloud; voxels_per_metre: resolution of the
+ * distance-bound grid (50 = 2 cm); point_radius: radius of every cloud point
+ * (planning/config.py:13).  max_voxels bounds the grid memory (0 = default). */
+int tg_env_create(tg_env** out, int device, int64_t max_points, float voxels_per_metre,
+                  float point_radius, int64_t max_voxels);
+int tg_env_destroy(tg_env* env);
+
+/* Replace the cloud: clear_pointclouds + add_pointcloud (vamp_preview.py:183-240).
+ * xyz: DEVICE, n x 3 f32 (n may be 0 = empty world).  Builds the sorted cell table
+ * and the distance-bound grid on `stream`.  Synchronises the stream once (cloud
+ * bounds are read back to size the grids) unless fixed bounds were set.          */
+int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stream);
+/* Same, xyz on the HOST (pageable or pinned).                                    */
+int tg_env_build_host(tg_env* env, const float* xyz, int64_t n, void* stream);
+/* Fix the workspace box [lo, hi] (HOST, 3 floats each): tg_env_build then never
+ * synchronises (CUDA-graph capturable); points outside are ignored and counted
+ * in tg_env_stats.  Pass NULL, NULL to return to automatic bounds.               */
+int tg_env_set_bounds(tg_env* env, const float* lo, const float* hi);
+/* point radius used by the next build (add_pointcloud(point_radius=...), :205-209) */
+int tg_env_set_point_radius(tg_env* env, float point_radius);
+
+/* add_sphere / clear_spheres (vamp_preview.py:242-255): xyzr HOST, n x 4 f32.    */
+int tg_env_set_obstacles(tg_env* env, const float* xyzr, int n, void* stream);
+/* attach_to_eef / detach_from_eef (vamp_preview.py:257-304): spheres xyzr HOST
+ * (n x 4, positions in the attachment frame), offset position (3) and quaternion
+ * [x,y,z,w] (4) relative to gripper_link, HOST.  n = 0 detaches.                 */
+int tg_env_set_attachment(tg_env* env, const float* xyzr, int n, const float* offset_pos,
+                          const float* offset_quat, void* stream);
+
+/* Structure hand-off for multi-GPU (cloud structure replicated on every rank):
+ * export gives a contiguous DEVICE blob + its size; import adopts a blob that was
+ * broadcast into `blob` on this device.                                         */
+int tg_env_export(tg_env* env, void** blob, size_t* bytes);
+int tg_env_import(tg_env* env, const void* blob, size_t bytes, void* stream);
+size_t tg_env_blob_capacity(const tg_env* env);
+/* DEVICE address of the env's own blob storage (valid for the env's lifetime): a
+ * receiving rank lets NCCL write straight into it, then calls tg_env_import on it. */
+int tg_env_blob_ptr(tg_env* env, void** blob);
+
+/* stats (HOST out, 8 doubles): n_points, n_dropped, grid nx, ny, nz, cells,
+ * voxels_per_metre actually used, slack [m].                                    */
+int tg_env_stats(const tg_env* env, double* out8);
+
+/* ---- forward kinematics (fk_numpy.py:32-157, fk_torch.py:119-283) ------------- */
+/* World centres of the 111 spheres in the reference's sphere order; head2 may be
+ * NULL (= 0, 0: the planner's model).  arm B x 8, base B x 3, head2 B x 2,
+ * centres B x 111 x 3, all DEVICE f32.                                          */
+int tg_fk_spheres(const float* arm, const float* base, const float* head2, int64_t B,
+                  float* centres, void* stream);
+/* Link frames in base_link: q10 B x 10 -> frames B x 15 x 4 x 4 (row-major) f32,
+ * link order = fk_numpy's (see tygrit_b200/fetch_model.py LINK_NAMES).           */
+int tg_fk_frames(const float* q10, int64_t B, float* frames, void* stream);
+
+/* ---- verdicts ------------------------------------------------------------------ */
+/* validate_whole_body_config for a batch (vamp_preview.py:159-163,328-338).
+ * valid: DEVICE B bytes.  clearance: DEVICE B f32 or NULL; when given it receives
+ * min(exact clearance, clearance_cap) (cap = 0.25 m).                            */
+int tg_check_configs(tg_env* env, const float* arm, const float* base, int64_t B,
+                     uint8_t* valid, float* clearance, void* stream);
+/* Motion-edge validation at fixed resolution (VAMP validate_motion, used inside
+ * planner_func / simplify, planning/fetch/algorithms.py:37,51): edge e runs from
+ * (arm0,base0)[e] to (arm1,base1)[e]; n = max(ceil(|delta| * resolution / rake),1)
+ * blocks of `rake` samples, t_k = k/(rake n), k = 1..rake n.  valid: DEVICE E bytes.
+ * n_checks (DEVICE int64[1] or NULL) receives sum_e rake*n_e.                    */
+int tg_check_edges(tg_env* env, const float* arm0, const float* base0, const float* arm1,
+                   const float* base1, int64_t E, int rake, float resolution, uint8_t* valid,
+                   int64_t* n_checks, void* stream);
+
+/* HOST-buffer variants (the reference-facing calls: numpy in, numpy out).  They
+ * stage through pinned memory in chunks, overlap copies with the kernels, and
+ * return after the results are in `valid` (synchronous).                        */
+int tg_check_configs_host(tg_env* env, const float* arm, const float* base, int64_t B,
+                          uint8_t* valid, float* clearance);
+int tg_check_edges_host(tg_env* env, const float* arm0, const float* base0, const float* arm1,
+                        const float* base1, int64_t E, int rake, float resolution,
+                        uint8_t* valid, int64_t* n_checks);
+
+/* counters of the last check call on this env (HOST out, 4 int64): phase-1
+ * definite collisions, ambiguous items resolved by the exact narrow phase,
+ * queue overflows handled inline, kernels launched.                              */
+int tg_env_counters(tg_env* env, int64_t* out4, void* stream);
+
+/* Device-time instrumentation for benchmarking: when on, tg_check_configs brackets its
+ * phase-1 (FK + grid classification) and phase-2 (exact narrow phase) launches with CUDA
+ * events on the launching stream.  tg_env_timing_read waits for them and returns
+ * {phase-1 ms, phase-2 ms, launch pairs} accumulated since the last read (HOST out, 3 doubles). */
+int tg_env_set_timing(tg_env* env, int on);
+int tg_env_timing_read(tg_env* env, double* out3);
+
+/* ---- robot self-filter (kinematics/robot_filter.py:13-64) ---------------------- */
+/* keep[i] = 1 iff no centre c has |p_i - c|^2 < radius^2 (f32, no FMA contraction:
+ * bit-identical to the reference).  points N x 3, centres S x 3, keep N bytes,
+ * all DEVICE.                                                                    */
+int tg_filter_points(const float* points, int64_t N, const float* centres, int S, float radius,
+                     uint8_t* keep, void* stream);
+/* Batched depth self-filter: for every robot state s (states S x 13 DEVICE f32:
+ * x, y, theta, q0..q7, head_pan, head_tilt) back-project depth[s] (S x H x W DEVICE
+ * f32, stride-decimated like utils/depth.py:32-49 with K HOST 3x3 f64), transform by
+ * the head-camera pose (kinematics/fetch/camera.py:25-58) and test against the 111
+ * spheres at `radius`.  mask: DEVICE S x H' x W' bytes: 1 = keep (valid depth in
+ * [zmin, zmax] and outside the robot), 0 = dropped.  world (DEVICE S x H' x W' x 3
+ * f32 or NULL) receives the world points.                                        */
+int tg_self_filter_depth(const float* depth, int H, int W, int stride, const double* K,
+                         const float* states, int64_t S, float radius, float zmin, float zmax,
+                         uint8_t* mask, float* world, void* stream);
+
+/* ---- synthetic input (benchmark support, not part of the reference surface) ----- */
+/* Analytic head-camera depth frames: rays against the 8 x 6 x 2.6 m room shell, `nb`
+ * furniture boxes (DEVICE nb x 6: lo xyz, hi xyz; nb <= 64) and the robot's own 111
+ * spheres, ~2 % pixels zeroed.  states DEVICE S x 13, K HOST 3x3 f64, depth DEVICE
+ * S x H x W f32.  Stands in for the ManiSkill/SAPIEN renderer (no graphics stack).   */
+int tg_synth_depth(const float* states, int64_t S, const float* boxes, int nb, int H, int W,
+                   const double* K, float reserved, uint64_t seed, float* depth, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TYGRIT_B200_H */

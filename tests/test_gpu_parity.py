@@ -1,0 +1,365 @@
+"""GPU: parity of the CUDA path (through the C ABI) with the oracle.
+
+Bar: verdicts / masks bit-exact for every configuration, edge or point whose fp64 clearance
+satisfies |clearance| > 1e-5 m; FK sphere centres within 1e-6 m (fp32) — BASELINE.json north_star.
+"""
+
+from __future__ import annotations
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import cchecker, collide, fk as ofk, ingest as oin
+from tygrit_b200 import engine, synth
+from tygrit_b200.engine import CollisionWorld
+
+pytestmark = pytest.mark.gpu
+BAND = 1e-5
+FK_TOL = 1e-6
+
+
+def _cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+@pytest.fixture(scope="module")
+def tabletop():
+    cloud = synth.tabletop_cloud(50_000)
+    w = CollisionWorld(max_points=1 << 20)
+    w.build(_cuda(cloud))
+    return cloud, w, cchecker.CCloud(cloud)
+
+
+@pytest.fixture(scope="module")
+def room():
+    cloud = synth.room_cloud(200_000)
+    w = CollisionWorld(max_points=1 << 20)
+    w.build(_cuda(cloud))
+    return cloud, w, cchecker.CCloud(cloud)
+
+
+# ------------------------------------------------------------------ FK
+def test_fk_frames_vs_reference_golden(golden):
+    g = golden("fk.npz")
+    fr = engine.fk_frames(_cuda(g["q10"].astype(np.float32))).cpu().numpy()
+    assert fr.shape == (len(g["q10"]), 15, 4, 4)
+    ref = ofk.link_frames_4x4(g["q10"].astype(np.float32))     # same f32-rounded inputs, fp64 maths
+    assert np.abs(fr - ref).max() <= FK_TOL
+    assert np.abs(fr - g["frames"]).max() <= 1e-5              # reference's own torch-vs-numpy tolerance
+
+
+def test_fk_sphere_centres_within_1e6():
+    arm, base = synth.random_configs(100_000)
+    c = engine.fk_spheres(_cuda(arm), _cuda(base)).cpu().numpy()
+    ref = cchecker.centres_f64(arm, base)
+    err = np.abs(c - ref).max()
+    assert err <= FK_TOL, err
+    st = synth.random_states(4096)
+    c = engine.fk_spheres(_cuda(st[:, 3:11]), _cuda(st[:, :3]), _cuda(st[:, 11:13])).cpu().numpy()
+    ref = cchecker.centres_f64(st[:, 3:11], st[:, :3], st[:, 11:13])
+    assert np.abs(c - ref).max() <= FK_TOL
+
+
+def test_batch_fk_solver_protocol(golden):
+    from tygrit_b200.fk import create_fk_solver
+
+    g = golden("fk.npz")
+    solver = create_fk_solver("fetch", "fk_batch")
+    assert solver.base_frame == "base_link"
+    out = solver.solve(_cuda(g["q10"].astype(np.float32)))
+    assert set(out) == set(g["link_names"]) and out["gripper_link"].shape == (len(g["q10"]), 4, 4)
+    np.testing.assert_allclose(out["gripper_link"][0, :3, 3].cpu().numpy(), [1.1281, 0, 0.78601], atol=1e-4)
+    with pytest.raises(RuntimeError):
+        solver.solve(torch.zeros(2, 10))
+
+
+# ------------------------------------------------------------------ config verdicts
+def _assert_verdicts(valid, cl, what=""):
+    valid = np.asarray(valid).astype(bool)
+    decisive = np.abs(cl) > BAND
+    bad = np.flatnonzero((valid != (cl > 0)) & decisive)
+    assert bad.size == 0, f"{what}: {bad.size} verdict mismatches outside the band, e.g. idx {bad[:5]} clearance {cl[bad[:5]]}"
+
+
+def test_c1_tabletop_4096_configs(tabletop):
+    """BASELINE config[0]: 4096 random configs vs the 50k-point tabletop cloud."""
+    cloud, w, cc = tabletop
+    arm, base = synth.random_configs(4096, base_box=(-1, 1, -1, 1))
+    cl = collide.CloudOracle(cloud).config_clearance(arm, base)         # numpy/cKDTree oracle
+    valid, clr = w.check_configs(_cuda(arm), _cuda(base), clearance=True)
+    _assert_verdicts(valid.cpu().numpy(), cl, "C1")
+    assert 0.3 < valid.float().mean().item() < 0.8
+    got = clr.cpu().numpy()
+    np.testing.assert_allclose(got, np.minimum(cl, 0.25), atol=3e-6)
+    c = w.counters()
+    assert c["narrow_items"] > 0 and c["definite_collisions"] > 0     # both phases were exercised
+
+
+def test_room_configs_vs_c_oracle(room):
+    cloud, w, cc = room
+    arm, base = synth.random_configs(50_000, seed=7)
+    cl = cc.clearance(arm, base)
+    valid = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    _assert_verdicts(valid, cl, "room")
+    assert 0.05 < valid.mean() < 0.6
+
+
+def test_ragged_and_degenerate_batches(room):
+    cloud, w, cc = room
+    arm, base = synth.random_configs(1000, seed=3)
+    full = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    for n in (0, 1, 31, 33, 127, 129, 999):
+        part = w.check_configs(_cuda(arm[:n]), _cuda(base[:n])).cpu().numpy()
+        assert np.array_equal(part, full[:n])
+    # far outside the grid: nothing to hit
+    far = base.copy()
+    far[:, :2] += 500.0
+    assert w.check_configs(_cuda(arm), _cuda(far)).all()
+    # NaN configuration must not crash (verdict unspecified)
+    bad = arm.copy()
+    bad[0, 3] = np.nan
+    w.check_configs(_cuda(bad), _cuda(base))
+    torch.cuda.synchronize()
+
+
+def test_empty_single_and_nonfinite_clouds():
+    w = CollisionWorld(max_points=4096)
+    arm, base = synth.random_configs(500, seed=5)
+    w.build(np.empty((0, 3), np.float32))
+    assert w.check_configs(_cuda(arm), _cuda(base)).all()           # empty world: everything is free
+    # tuck configuration at the origin is valid in an empty environment (test/test_planner.py:72-78)
+    tuck = np.array([[0.0, 1.32, 1.40, -0.2, 1.72, 0.0, 1.66, 0.0]], np.float32)
+    assert w.check_configs_host(tuck, np.zeros((1, 3), np.float32))[0] == 1
+    one = np.array([[0.9, 0.0, 0.6]], np.float32)
+    w.build(one)
+    cl = collide.CloudOracle(one).config_clearance(arm, base * np.array([0.3, 0.3, 1], np.float32))
+    v = w.check_configs(_cuda(arm), _cuda(base * np.array([0.3, 0.3, 1], np.float32))).cpu().numpy()
+    _assert_verdicts(v, cl, "single point")
+    assert (cl <= 0).any()
+    dirty = np.vstack([one, [[np.nan, 0, 0]], [[np.inf, 1, 1]]]).astype(np.float32)
+    w.build(dirty)
+    v2 = w.check_configs(_cuda(arm), _cuda(base * np.array([0.3, 0.3, 1], np.float32))).cpu().numpy()
+    assert np.array_equal(v, v2) and w.stats()["n_dropped"] == 2
+    w.close()
+
+
+def test_obstacles_and_attachment(tabletop):
+    cloud, _, _ = tabletop
+    w = CollisionWorld(max_points=1 << 17)
+    w.build(cloud)
+    arm, base = synth.random_configs(3000, seed=11, base_box=(-1, 1, -1, 1))
+    obs = np.array([[0.6, 0.3, 1.0, 0.12], [0.2, -0.5, 0.5, 0.2]], np.float32)
+    att = {"spheres": np.array([[0.1, 0.0, 0.0, 0.04], [0.18, 0.02, 0.0, 0.03]]), "pos": (0.02, 0.0, 0.01),
+           "quat": (0.0, 0.3826834, 0.0, 0.9238795)}
+    w.set_obstacles(obs)
+    w.set_attachment(att["spheres"], att["pos"], att["quat"])
+    orc = collide.CloudOracle(cloud, obstacles=obs)
+    cl = orc.config_clearance(arm, base, attachment=att)
+    cl_plain = collide.CloudOracle(cloud).config_clearance(arm, base)
+    v = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    _assert_verdicts(v, cl, "extras")
+    assert ((cl <= 0) & (cl_plain > 0)).sum() > 10                  # the extras changed some verdicts
+    w.set_obstacles(np.empty((0, 4), np.float32))
+    w.set_attachment(np.empty((0, 4), np.float32))
+    _assert_verdicts(w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy(), cl_plain, "extras cleared")
+    w.close()
+
+
+def test_point_radius_and_coarse_grid(tabletop):
+    cloud, _, cc = tabletop
+    arm, base = synth.random_configs(4000, seed=13, base_box=(-1, 1, -1, 1))
+    for vpm, r_pt in ((25.0, 0.03), (50.0, 0.0), (80.0, 0.05)):
+        w = CollisionWorld(max_points=1 << 16, voxels_per_metre=vpm, point_radius=r_pt)
+        w.build(cloud)
+        cl = cchecker.CCloud(cloud, point_radius=r_pt).clearance(arm, base)
+        _assert_verdicts(w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy(), cl, f"vpm={vpm} r={r_pt}")
+        w.close()
+    # a world too big for the requested resolution is coarsened, never truncated
+    w = CollisionWorld(max_points=1 << 16, voxels_per_metre=100.0, max_voxels=1 << 20)
+    w.build(cloud)
+    assert w.stats()["voxels_per_metre"] < 100.0
+    _assert_verdicts(w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy(), cc.clearance(arm, base), "coarsened")
+    w.close()
+
+
+def test_host_api_matches_device_api_and_chunks(room):
+    cloud, w, cc = room
+    arm, base = synth.random_configs(1_300_000, seed=21)              # > one 1M pipeline chunk
+    dev = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    host = w.check_configs_host(arm, base)
+    assert np.array_equal(dev, host)
+    sub = np.random.default_rng(0).choice(len(arm), 20_000, replace=False)
+    _assert_verdicts(host[sub], cc.clearance(arm[sub], base[sub]), "host api")
+    torch.cuda.synchronize()
+    again = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    assert np.array_equal(dev, again)                                  # deterministic
+
+
+def test_structure_export_import(room):
+    cloud, w, cc = room
+    arm, base = synth.random_configs(20_000, seed=31)
+    ref = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    n = w.used_bytes()
+    w2 = CollisionWorld(max_points=1 << 20)
+    w2.blob_view(n).copy_(w.blob_view(n))                              # what an NCCL broadcast would do
+    torch.cuda.synchronize()
+    w2.adopt_blob(n)
+    assert np.array_equal(w2.check_configs(_cuda(arm), _cuda(base)).cpu().numpy(), ref)
+    w3 = CollisionWorld(max_points=1 << 20)
+    w3.import_blob(w.blob_view(n).clone())
+    assert np.array_equal(w3.check_configs(_cuda(arm), _cuda(base)).cpu().numpy(), ref)
+    w2.close()
+    w3.close()
+
+
+# ------------------------------------------------------------------ edges
+def test_c2_edges_vs_oracle(room):
+    """BASELINE config[1] at oracle-sized scale: random Fetch edges at VAMP default resolution."""
+    cloud, w, cc = room
+    a0, b0, a1, b1 = synth.random_edges(3000, seed=42)
+    cl, ns = cc.edge_clearance(a0, b0, a1, b1)
+    valid, nchk = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1), count=True)
+    assert int(nchk.item()) == int(ns.sum())
+    _assert_verdicts(valid.cpu().numpy(), cl, "C2 edges")
+    # short RRT-like edges + whole-body edges (base moves too)
+    a0, b0, a1, b1 = synth.random_edges(3000, seed=43, rrt_like=True)
+    b1 = b1 + np.random.default_rng(1).normal(0, 0.1, b1.shape).astype(np.float32)
+    cl, ns = cc.edge_clearance(a0, b0, a1, b1)
+    valid, nchk = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1), count=True)
+    assert int(nchk.item()) == int(ns.sum())
+    _assert_verdicts(valid.cpu().numpy(), cl, "short edges")
+    assert 0 < valid.sum() < len(valid)
+    hv, hn = w.check_edges_host(a0, b0, a1, b1)
+    assert np.array_equal(hv, valid.cpu().numpy()) and hn == int(ns.sum())
+
+
+def test_edge_properties(room):
+    cloud, w, cc = room
+    arm, base = synth.random_configs(5000, seed=51)
+    cfg_ok = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    # a zero-length edge samples its end point rake times: same verdict as the configuration
+    e_ok = w.check_edges(_cuda(arm), _cuda(base), _cuda(arm), _cuda(base)).cpu().numpy()
+    assert np.array_equal(cfg_ok, e_ok)
+    # a valid edge implies a valid end point (end included, start excluded)
+    a0, b0, a1, b1 = synth.random_edges(5000, seed=52, rrt_like=True)
+    ev = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1)).cpu().numpy().astype(bool)
+    end_ok = w.check_configs(_cuda(a1), _cuda(b1)).cpu().numpy().astype(bool)
+    assert not (ev & ~end_ok).any()
+
+
+# ------------------------------------------------------------------ self-filter
+def test_filter_points_bit_exact_vs_reference_golden(golden):
+    g = golden("self_filter.npz")
+    for i in range(int(g["n_cases"])):
+        c32 = oin.filter_centres_f32(g[f"q{i}"][None], g[f"base{i}"][None])[0]
+        keep = engine.filter_points_mask(_cuda(g[f"pts{i}"]), _cuda(c32), float(g[f"radius{i}"])).cpu().numpy().astype(bool)
+        assert np.array_equal(keep, g[f"keep{i}"])                     # bit-exact, band included
+
+
+def test_filter_robot_points_dropin():
+    """Mirrors test/test_robot_filter.py of the reference."""
+    from tygrit_b200.fetch_model import fetch_spheres_dict
+    from tygrit_b200.robot_filter import filter_robot_points
+
+    T = ofk.link_frames_4x4(np.zeros((1, 10)))[0]
+    from oracle.fetch_model import LINK_NAMES
+
+    poses = {n: T[i] for i, n in enumerate(LINK_NAMES)}
+    sph = fetch_spheres_dict()
+    assert filter_robot_points(np.empty((0, 3), np.float32), poses, sph).shape == (0, 3)
+    far = np.array([[5, 5, 1], [10, 0, 0.5], [-3, -3, 2]], np.float32)
+    assert filter_robot_points(far, poses, sph).shape[0] == 3
+    pts = np.vstack([[[0, 0, 0.2]], [[5, 5, 1]]]).astype(np.float32)
+    out = filter_robot_points(pts, poses, sph, sphere_radius=0.15)
+    assert out.shape[0] == 1 and out.dtype == np.float32 and np.allclose(out[0], [5, 5, 1])
+    arm_pts = np.vstack([poses["gripper_link"][:3, 3], poses["elbow_flex_link"][:3, 3], [5, 5, 1]]).astype(np.float32)
+    assert filter_robot_points(arm_pts, poses, sph, sphere_radius=0.12).shape[0] == 1
+    big = np.random.default_rng(42).uniform(-5, 5, (10_000, 3)).astype(np.float32)
+    n = filter_robot_points(big, poses, sph).shape[0]
+    assert 0 < n < 10_000
+    t = filter_robot_points(_cuda(big), poses, sph)
+    assert t.is_cuda and t.shape[0] == n
+
+
+def _numpy_depth(states, boxes, H, W, K, seed):
+    """numpy twin of csrc/synth.cu (without the invalid-pixel hash): analytic ray casting."""
+    from oracle import fetch_model as om
+
+    out = np.zeros((len(states), H, W), np.float32)
+    for s, st in enumerate(states.astype(np.float64)):
+        cam = ofk.camera_pose(st[None, 3:11], st[None, 11:13], st[None, :3])[0]
+        cen = ofk.sphere_centres(st[None, 3:11], st[None, :3], st[None, 11:13])[0]
+        v, u = np.mgrid[0:H, 0:W]
+        d = np.stack([(u - K[0, 2]) / K[0, 0], (v - K[1, 2]) / K[1, 1], np.ones_like(u, float)], -1) @ cam[:3, :3].T
+        o = cam[:3, 3]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            t = np.where(d > 0, (np.array([4.0, 3.0, 2.6]) - o) / d, np.where(d < 0, (np.array([-4.0, -3.0, 0.0]) - o) / d, 1e30))
+            best = t.min(-1)
+            for lo, hi in boxes:
+                ta, tb = (np.array(lo) - o) / d, (np.array(hi) - o) / d
+                t0 = np.maximum(np.minimum(ta, tb).max(-1), 0.0)
+                t1 = np.minimum(np.maximum(ta, tb).min(-1), best)
+                best = np.where((t0 <= t1) & (t0 > 0), t0, best)
+            dd = (d * d).sum(-1)
+            for c, r in zip(cen, om.SPHERE_LOCAL[:, 3]):
+                l = c - o
+                bq = d @ l
+                disc = bq * bq - dd * (l @ l - r * r)
+                tt = (bq - np.sqrt(np.maximum(disc, 0))) / dd
+                best = np.where((disc >= 0) & (tt > 0.02) & (tt < best), tt, best)
+        out[s] = best
+    return out
+
+
+def test_self_filter_depth_batch_vs_oracle():
+    """BASELINE config[2] at oracle-sized scale: batched depth self-filter, FK on the GPU."""
+    H, W = 120, 160
+    K = synth.HEAD_CAMERA_K.copy()
+    K[:2] *= W / 640.0
+    states = synth.random_states(6, seed=9)
+    states[:, 11] = np.clip(states[:, 11], -0.6, 0.6)
+    states[:, 12] = 0.9                                              # look down at the arm
+    boxes = synth.room_boxes()
+    depth = _numpy_depth(states, boxes, H, W, K, 0)
+    depth[:, ::7, ::5] = 0.0
+    depth[0, 3, 4] = np.nan
+    for stride in (1, 4):
+        mask, world = engine.self_filter_depth(_cuda(depth), K, _cuda(states), 0.08, (0.2, 3.0), stride, want_world=True)
+        mask, world = mask.cpu().numpy().astype(bool), world.cpu().numpy()
+        n_removed = 0
+        for s in range(len(states)):
+            T = ofk.camera_pose(states[s:s + 1, 3:11], states[s:s + 1, 11:13], states[s:s + 1, :3])[0]
+            pw, keep = oin.depth_to_world(depth[s], K, T, (0.2, 3.0), stride)
+            np.testing.assert_allclose(world[s][keep], pw, atol=5e-6)   # fp32 camera pose vs fp64 pose
+            c64 = ofk.sphere_centres(states[s:s + 1, 3:11], states[s:s + 1, :3], states[s:s + 1, 11:13])[0]
+            signed = oin.self_filter_signed_band(pw, c64, 0.08)
+            expect = np.zeros(keep.shape, bool)
+            expect[keep] = signed >= 0
+            decisive = np.ones(keep.shape, bool)
+            decisive[keep] = np.abs(signed) > BAND
+            assert np.array_equal(mask[s][decisive], expect[decisive])
+            assert not mask[s][~keep].any()                             # invalid depth is never kept
+            n_removed += int((signed < 0).sum())
+        assert n_removed > 50                                           # the robot was really in view
+
+
+def test_synth_depth_kernel_matches_numpy_twin():
+    from tygrit_b200 import _native as N
+
+    H, W = 60, 80
+    K = synth.HEAD_CAMERA_K.copy()
+    K[:2] *= W / 640.0
+    states = synth.random_states(3, seed=4)
+    boxes = synth.room_boxes()
+    bx = _cuda(np.array([[*lo, *hi] for lo, hi in boxes], np.float32))
+    out = torch.empty(3, H, W, device="cuda")
+    st = _cuda(states)
+    Kc = np.ascontiguousarray(K)
+    N.check(N.lib().tg_synth_depth(st.data_ptr(), 3, bx.data_ptr(), len(boxes), H, W, Kc.ctypes.data, 0.0, 1,
+                                   out.data_ptr(), None), "tg_synth_depth")
+    got = out.cpu().numpy()
+    ref = _numpy_depth(states, boxes, H, W, K, 1)
+    ok = got > 0
+    assert 0.9 < ok.mean() < 0.995                                    # ~2 % invalid pixels
+    assert np.median(np.abs(got[ok] - ref[ok])) < 1e-4 and (np.abs(got[ok] - ref[ok]) < 1e-2).mean() > 0.98

@@ -1,0 +1,663 @@
+// env.cu — K1: point cloud -> sorted cell table + distance-bound grid, all in HBM.
+//
+// Replaces the CAPT rebuild behind VampPreviewPlanner.update_environment / add_pointcloud
+// (TyGrit/planning/fetch/vamp_preview.py:183-240), which the reference pays on every scheduler
+// iteration through a Python list-of-lists (pts.tolist(), :222-224).
+//
+// Pipeline on the caller's stream (HBM-bound, 28 B/point compulsory + 4 B/voxel for the grid):
+//   k_bounds      min/max of the finite points (skipped with fixed bounds)
+//   k_count       per point: cell key, rank inside its cell (global atomic), mark its voxel
+//   k_scan_*      exclusive scan of the cell histogram -> cell_start
+//   k_scatter     counting-sort scatter into float4 points (x fastest key => rows are contiguous)
+//   k_edt_x/y/z   exact truncated Euclidean distance transform between voxel centres,
+//                 shared-memory tiles, quantised to one byte per voxel
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "fetch_model.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// error text
+// ------------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+void tg_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* tg_last_error(void) { return g_err; }
+extern "C" int tg_version(void) { return 100; }
+
+// ------------------------------------------------------------------------------------------------
+// kernels
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int f2ord(float f) {  // monotone float -> int
+  int i = __float_as_int(f);
+  return i >= 0 ? i : i ^ 0x7FFFFFFF;
+}
+static inline float ord2f(int i) {
+  int j = i >= 0 ? i : i ^ 0x7FFFFFFF;
+  float f;
+  memcpy(&f, &j, 4);
+  return f;
+}
+
+__global__ void k_bounds_init(int* b) {
+  if (threadIdx.x < 3) b[threadIdx.x] = 0x7FFFFFFF;
+  else if (threadIdx.x < 6) b[threadIdx.x] = (int)0x80000000;
+  else if (threadIdx.x < 8) b[threadIdx.x] = 0;
+}
+
+__global__ void __launch_bounds__(256) k_bounds(const float* __restrict__ xyz, int n, int* __restrict__ b) {
+  int lo[3] = {0x7FFFFFFF, 0x7FFFFFFF, 0x7FFFFFFF};
+  int hi[3] = {(int)0x80000000, (int)0x80000000, (int)0x80000000};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+    if (isfinite(x) && isfinite(y) && isfinite(z)) {
+      lo[0] = min(lo[0], f2ord(x)); hi[0] = max(hi[0], f2ord(x));
+      lo[1] = min(lo[1], f2ord(y)); hi[1] = max(hi[1], f2ord(y));
+      lo[2] = min(lo[2], f2ord(z)); hi[2] = max(hi[2], f2ord(z));
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    for (int o = 16; o; o >>= 1) {
+      lo[a] = min(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+      hi[a] = max(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+    }
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      atomicMin(&b[a], lo[a]);
+      atomicMax(&b[3 + a], hi[a]);
+    }
+  }
+}
+
+// per point: cell key + rank in cell; mark the df voxel.  Points that are not finite or fall
+// outside the grids are dropped (key = 0xFFFFFFFF) and counted.
+__global__ void __launch_bounds__(256)
+k_count(const float* __restrict__ xyz, int n, TgGrid g, uint8_t* __restrict__ occ, uint32_t* __restrict__ cell_count,
+        uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int* __restrict__ dropped) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  uint32_t k = 0xFFFFFFFFu;
+  if (isfinite(x) && isfinite(y) && isfinite(z)) {
+    // df voxel: same arithmetic as the query side (one FMA-free multiply + magic add)
+    const float fx = fmaf(x, g.vpm, g.bias[0]), fy = fmaf(y, g.vpm, g.bias[1]), fz = fmaf(z, g.vpm, g.bias[2]);
+    const int cx = (int)floorf(x * g.cpm) - g.cm[0];
+    const int cy = (int)floorf(y * g.cpm) - g.cm[1];
+    const int cz = (int)floorf(z * g.cpm) - g.cm[2];
+    const bool in_df = fx >= TG_MAGIC && fx <= g.hi[0] && fy >= TG_MAGIC && fy <= g.hi[1] && fz >= TG_MAGIC && fz <= g.hi[2];
+    const bool in_cells = cx >= 0 && cx < g.cnx && cy >= 0 && cy < g.cny && cz >= 0 && cz < g.cnz;
+    if (in_df && in_cells) {
+      const unsigned v = (unsigned)__float_as_int(fx) + (unsigned)g.nx * (unsigned)__float_as_int(fy) +
+                         (unsigned)g.nxy * (unsigned)__float_as_int(fz) - g.idx_bias;
+      occ[v] = 1;
+      k = (uint32_t)((cz * g.cny + cy) * g.cnx + cx);
+      rank[i] = atomicAdd(&cell_count[k], 1u);
+    }
+  }
+  key[i] = k;
+  if (k == 0xFFFFFFFFu) atomicAdd(dropped, 1);
+}
+
+// ---- exclusive scan over the cell histogram (3 kernels, 2048 items per block) -------------------
+#define SCAN_ITEMS 2048
+__global__ void __launch_bounds__(256) k_scan_block_sums(const uint32_t* __restrict__ in, int n, uint32_t* __restrict__ sums) {
+  __shared__ uint32_t warp_sum[8];
+  const int base = blockIdx.x * SCAN_ITEMS;
+  uint32_t s = 0;
+  for (int j = threadIdx.x; j < SCAN_ITEMS; j += 256)
+    if (base + j < n) s += in[base + j];
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < 8; ++w) t += warp_sum[w];
+    sums[blockIdx.x] = t;
+  }
+}
+__global__ void __launch_bounds__(1024) k_scan_sums(uint32_t* sums, int nb) {  // single block, in place, exclusive
+  __shared__ uint32_t warp_tot[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < nb; base += 1024) {
+    const int i = base + threadIdx.x;
+    uint32_t v = i < nb ? sums[i] : 0, inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if ((threadIdx.x & 31) >= o) inc += t;
+    }
+    if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      uint32_t w = warp_tot[threadIdx.x], winc = w;
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, winc, o);
+        if (threadIdx.x >= o) winc += t;
+      }
+      warp_tot[threadIdx.x] = winc - w;  // exclusive warp offsets
+    }
+    __syncthreads();
+    const uint32_t excl = carry + warp_tot[threadIdx.x >> 5] + inc - v;
+    if (i < nb) sums[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = excl + v;
+    __syncthreads();
+  }
+}
+// out[i] = exclusive prefix; out[n] = total.  Block re-scans its 2048 items serially per thread (8 each).
+__global__ void __launch_bounds__(256)
+k_scan_apply(const uint32_t* __restrict__ in, int n, const uint32_t* __restrict__ sums, uint32_t* __restrict__ out) {
+  __shared__ uint32_t warp_tot[8];
+  const int base = blockIdx.x * SCAN_ITEMS + threadIdx.x * 8;
+  uint32_t v[8], s = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    v[j] = (base + j < n) ? in[base + j] : 0;
+    s += v[j];
+  }
+  uint32_t inc = s;
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if ((threadIdx.x & 31) >= o) inc += t;
+  }
+  if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  uint32_t off = sums[blockIdx.x];
+  for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) off += warp_tot[w];
+  uint32_t run = off + inc - s;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (base + j < n) out[base + j] = run;
+    run += v[j];
+    if (base + j == n - 1) out[n] = run;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_scatter(const float* __restrict__ xyz, int n, const uint32_t* __restrict__ key, const uint32_t* __restrict__ rank,
+          const uint32_t* __restrict__ cell_start, float4* __restrict__ pts) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t k = key[i];
+  if (k == 0xFFFFFFFFu) return;
+  pts[cell_start[k] + rank[i]] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], 0.f);
+}
+
+// ---- truncated exact EDT --------------------------------------------------------------------------
+// pass X: g1 = distance (voxels) to the nearest occupied voxel in the same x-row, 255 if none within W
+__global__ void __launch_bounds__(256) k_edt_x(const uint8_t* __restrict__ occ, uint8_t* __restrict__ g1, int nx, int rows, int W) {
+  extern __shared__ uint8_t srow[];  // 8 rows of nx bytes
+  const int r0 = blockIdx.x * 8;
+  for (int j = threadIdx.x; j < 8 * nx; j += 256) {
+    const int r = r0 + j / nx;
+    srow[j] = r < rows ? occ[(size_t)r0 * nx + j] : 0;
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 8 * nx; j += 256) {
+    const int rr = j / nx, x = j - rr * nx;
+    if (r0 + rr >= rows) break;
+    const uint8_t* row = srow + rr * nx;
+    int d = 255;
+    if (row[x]) d = 0;
+    else
+      for (int k = 1; k <= W; ++k) {
+        if ((x - k >= 0 && row[x - k]) || (x + k < nx && row[x + k])) { d = k; break; }
+      }
+    g1[(size_t)r0 * nx + j] = (uint8_t)d;
+  }
+}
+
+// pass Y: g2 = min_y' g1(y')^2 + (y-y')^2  (u16, 65535 = none)
+__global__ void __launch_bounds__(256) k_edt_y(const uint8_t* __restrict__ g1, uint16_t* __restrict__ g2, int nx, int ny, int W) {
+  extern __shared__ uint8_t tile[];  // [ny][32]
+  const int x0 = blockIdx.x * 32, z = blockIdx.y;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const size_t slab = (size_t)z * nx * ny;
+  for (int y = ty; y < ny; y += 8) tile[y * 32 + tx] = (x0 + tx < nx) ? g1[slab + (size_t)y * nx + x0 + tx] : 255;
+  __syncthreads();
+  if (x0 + tx >= nx) return;
+  for (int y = ty; y < ny; y += 8) {
+    const int v0 = tile[y * 32 + tx];
+    int best = v0 == 255 ? 65535 : v0 * v0;
+    for (int k = 1; k <= W; ++k) {
+      const int k2 = k * k;
+      if (k2 >= best) break;
+      if (y - k >= 0) {
+        const int v = tile[(y - k) * 32 + tx];
+        if (v != 255) best = min(best, v * v + k2);
+      }
+      if (y + k < ny) {
+        const int v = tile[(y + k) * 32 + tx];
+        if (v != 255) best = min(best, v * v + k2);
+      }
+    }
+    g2[slab + (size_t)y * nx + x0 + tx] = (uint16_t)best;
+  }
+}
+
+// pass Z: d2 = min_z' g2(z') + (z-z')^2 ; code = d2 >= W^2 ? 255 : floor(sqrt(d2) * 255 / W)
+__global__ void __launch_bounds__(256)
+k_edt_z(const uint16_t* __restrict__ g2, uint8_t* __restrict__ df, int nx, int ny, int nz, int W) {
+  extern __shared__ uint16_t tilez[];  // [nz][32]
+  const int x0 = blockIdx.x * 32, y = blockIdx.y;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const size_t nxy = (size_t)nx * ny;
+  for (int z = ty; z < nz; z += 8) tilez[z * 32 + tx] = (x0 + tx < nx) ? g2[z * nxy + (size_t)y * nx + x0 + tx] : 65535;
+  __syncthreads();
+  if (x0 + tx >= nx) return;
+  const float scale = 255.0f / (float)W;
+  const int W2 = W * W;
+  for (int z = ty; z < nz; z += 8) {
+    int best = tilez[z * 32 + tx];
+    for (int k = 1; k <= W; ++k) {
+      const int k2 = k * k;
+      if (k2 >= best) break;
+      if (z - k >= 0) best = min(best, (int)tilez[(z - k) * 32 + tx] + k2);
+      if (z + k < nz) best = min(best, (int)tilez[(z + k) * 32 + tx] + k2);
+    }
+    int code = 255;
+    if (best < W2) code = min(254, (int)floorf(sqrtf((float)best) * scale));
+    df[z * nxy + (size_t)y * nx + x0 + tx] = (uint8_t)code;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static const double kEpsFp = 2e-5;  // metres: fp32 slop of centres / voxel index rounding
+
+static void tg_compute_thresholds(const TgGrid& g, TgThr* thr) {
+  const double q = g.q, slack = g.slack;
+  for (int j = 0; j < TG_N_SPHERES; ++j) {
+    const double R = (double)TGM_H_RADIUS_K[j] + (double)g.r_pt;
+    int fg = (int)floor((R + slack) / q) + 1;
+    int cl = (R - slack) > 0 ? (int)floor((R - slack) / q) - 1 : -1;
+    if (cl > 254) cl = 254;
+    if (cl < -1) cl = -1;
+    thr->free_ge[j] = fg;
+    thr->coll_le[j] = cl;
+  }
+}
+
+// choose grid geometry for the cloud box [lo, hi]; returns false if it cannot fit
+static bool tg_plan_grids(tg_env* env, const float lo[3], const float hi[3], TgGrid* g) {
+  double vpm = env->vpm_requested, cpm = env->cpm_requested;
+  const double r_need = 0.24 + (double)env->r_pt;  // largest robot sphere + point radius
+  for (int it = 0; it < 64; ++it) {
+    const double slack = sqrt(3.0) / vpm + kEpsFp;
+    int W = (int)ceil((r_need + slack + 0.004) * vpm) + 1;
+    if (W > 32) {  // window too wide for the transform: the grid is finer than useful
+      vpm *= 0.9;
+      continue;
+    }
+    int m[3], n[3];
+    double nvox = 1;
+    bool ok = true;
+    for (int a = 0; a < 3; ++a) {
+      m[a] = (int)floor((double)lo[a] * vpm) - (W + 3);
+      n[a] = (int)ceil((double)hi[a] * vpm) + (W + 3) - m[a] + 1;
+      if (n[a] > 1024 || abs(m[a]) > 4000000) ok = false;
+      nvox *= n[a];
+    }
+    if (!ok || nvox > (double)env->max_voxels) {
+      vpm *= 0.9;
+      if (vpm < 1.0) return false;
+      continue;
+    }
+    g->vpm = (float)vpm;
+    vpm = g->vpm;  // what the kernels will really use
+    g->window = W;
+    g->q = (float)((W / vpm) / 255.0);
+    g->slack = (float)(sqrt(3.0) / vpm + kEpsFp + 0.02 * g->q);
+    for (int a = 0; a < 3; ++a) {
+      g->bias[a] = TG_MAGIC - (float)m[a];
+      g->hi[a] = TG_MAGIC + (float)(n[a] - 1);
+    }
+    g->nx = n[0]; g->ny = n[1]; g->nz = n[2];
+    g->nxy = n[0] * n[1];
+    g->idx_bias = TG_MAGIC_BITS * (1u + (unsigned)g->nx + (unsigned)g->nxy);
+    break;
+  }
+  if (g->nx == 0) return false;
+  for (int it = 0; it < 64; ++it) {
+    int cm[3], cn[3];
+    double nc = 1;
+    for (int a = 0; a < 3; ++a) {
+      cm[a] = (int)floor((double)lo[a] * cpm) - 1;
+      cn[a] = (int)floor((double)hi[a] * cpm) - cm[a] + 2;
+      nc *= cn[a];
+    }
+    if (nc > (double)env->max_cells) {
+      cpm *= 0.9;
+      continue;
+    }
+    g->cpm = (float)cpm;
+    for (int a = 0; a < 3; ++a) g->cm[a] = cm[a];
+    g->cnx = cn[0]; g->cny = cn[1]; g->cnz = cn[2];
+    return true;
+  }
+  return false;
+}
+
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static void tg_layout(tg_env* env, TgGrid* g, TgHeader* h) {
+  const size_t nvox = (size_t)g->nx * g->ny * g->nz;
+  const size_t ncell = (size_t)g->cnx * g->cny * g->cnz;
+  h->off_df = TG_HEADER_BYTES;
+  h->off_cells = align256(h->off_df + nvox);
+  h->off_pts = align256(h->off_cells + 4 * (ncell + 1));
+  h->bytes = align256(h->off_pts + 16 * (size_t)g->n_points);
+  g->df = env->blob + h->off_df;
+  g->cell_start = (const uint32_t*)(env->blob + h->off_cells);
+  g->pts = (const float4*)(env->blob + h->off_pts);
+}
+
+extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float voxels_per_metre, float point_radius,
+                             int64_t max_voxels) {
+  TG_CHECK_ARG(out != nullptr, "tg_env_create: out is NULL");
+  TG_CHECK_ARG(max_points > 0 && max_points < (1ll << 31), "tg_env_create: max_points out of range");
+  TG_CHECK_ARG(voxels_per_metre >= 5.f && voxels_per_metre <= 100.f, "tg_env_create: voxels_per_metre must be in [5, 100]");
+  TG_CHECK_ARG(point_radius >= 0.f && point_radius < 1.f, "tg_env_create: point_radius out of range");
+  int ndev = 0;
+  TG_CUDA(cudaGetDeviceCount(&ndev));
+  TG_CHECK_ARG(device >= 0 && device < ndev, "tg_env_create: no such CUDA device");
+  TG_CUDA(cudaSetDevice(device));
+  tg_env* env = new tg_env();
+  memset(env, 0, sizeof(*env));
+  env->device = device;
+  env->timing_events = new std::vector<cudaEvent_t>();
+  env->max_points = max_points;
+  env->max_voxels = max_voxels > 0 ? max_voxels : (int64_t)64 << 20;
+  env->max_cells = env->max_voxels / 4;
+  env->vpm_requested = voxels_per_metre;
+  env->cpm_requested = voxels_per_metre * 0.5f;
+  env->r_pt = point_radius;
+  env->blob_capacity = TG_HEADER_BYTES + align256(env->max_voxels) + align256(4 * (env->max_cells + 1)) +
+                       align256(16 * (size_t)max_points) + 1024;
+  TG_CUDA(cudaMalloc(&env->blob, env->blob_capacity));
+  TG_CUDA(cudaMalloc(&env->g1, env->max_voxels));
+  TG_CUDA(cudaMalloc(&env->g2, 2 * env->max_voxels));
+  TG_CUDA(cudaMalloc(&env->cell_count, 4 * (env->max_cells + 1)));
+  TG_CUDA(cudaMalloc(&env->rank, 4 * max_points));
+  TG_CUDA(cudaMalloc(&env->key, 4 * max_points));
+  TG_CUDA(cudaMalloc(&env->scan_tmp, 4 * (env->max_cells / SCAN_ITEMS + 2)));
+  TG_CUDA(cudaMalloc(&env->bounds_dev, 8 * sizeof(int)));
+  TG_CUDA(cudaMallocHost(&env->bounds_host, 8 * sizeof(int)));
+  TG_CUDA(cudaMallocHost(&env->header_host, TG_HEADER_BYTES));
+  TG_CUDA(cudaMalloc(&env->extras_dev, sizeof(TgExtras)));
+  TG_CUDA(cudaMemset(env->extras_dev, 0, sizeof(TgExtras)));
+  env->queue_capacity = 1u << 22;  // 4M items = 256 MB
+  TG_CUDA(cudaMalloc(&env->items, (size_t)env->queue_capacity * sizeof(TgItem)));
+  TG_CUDA(cudaMalloc(&env->queue_count, 64));
+  TG_CUDA(cudaMalloc(&env->counters_dev, sizeof(TgCounters)));
+  TG_CUDA(cudaMemset(env->counters_dev, 0, sizeof(TgCounters)));
+  TG_CUDA(cudaMallocHost(&env->counters_host, sizeof(TgCounters)));
+  cudaDeviceProp prop;
+  TG_CUDA(cudaGetDeviceProperties(&prop, device));
+  env->sm_count = prop.multiProcessorCount;
+  // empty world until the first build
+  env->grid.empty = 1;
+  env->grid.r_pt = point_radius;
+  TG_CUDA(cudaFuncSetAttribute(k_edt_z, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * 32 * 2));
+  *out = env;
+  return TG_OK;
+}
+
+extern "C" int tg_env_destroy(tg_env* env) {
+  if (!env) return TG_OK;
+  cudaSetDevice(env->device);
+  cudaFree(env->blob); cudaFree(env->g1); cudaFree(env->g2); cudaFree(env->cell_count);
+  cudaFree(env->rank); cudaFree(env->key); cudaFree(env->scan_tmp); cudaFree(env->bounds_dev);
+  cudaFree(env->xyz_stage); cudaFree(env->extras_dev); cudaFree(env->items); cudaFree(env->queue_count);
+  cudaFree(env->counters_dev);
+  cudaFreeHost(env->bounds_host); cudaFreeHost(env->header_host); cudaFreeHost(env->counters_host);
+  for (int i = 0; i < 2; ++i) {
+    if (env->streams[i]) cudaStreamDestroy(env->streams[i]);
+    if (env->events[i]) cudaEventDestroy(env->events[i]);
+    cudaFreeHost(env->pin_in[i]); cudaFreeHost(env->pin_out[i]); cudaFreeHost(env->pin_clear[i]);
+    cudaFree(env->dev_in[i]); cudaFree(env->dev_out[i]); cudaFree(env->dev_clear[i]);
+  }
+  if (env->timing_events) {
+    for (cudaEvent_t e : *env->timing_events) cudaEventDestroy(e);
+    delete env->timing_events;
+  }
+  delete env;
+  return TG_OK;
+}
+
+extern "C" int tg_env_set_bounds(tg_env* env, const float* lo, const float* hi) {
+  TG_CHECK_ARG(env != nullptr, "tg_env_set_bounds: env is NULL");
+  if (!lo || !hi) {
+    env->fixed_bounds = false;
+    return TG_OK;
+  }
+  for (int a = 0; a < 3; ++a) {
+    TG_CHECK_ARG(isfinite(lo[a]) && isfinite(hi[a]) && hi[a] > lo[a], "tg_env_set_bounds: need finite lo < hi");
+    env->lo[a] = lo[a];
+    env->hi[a] = hi[a];
+  }
+  env->fixed_bounds = true;
+  return TG_OK;
+}
+
+extern "C" int tg_env_set_point_radius(tg_env* env, float r) {
+  TG_CHECK_ARG(env != nullptr && r >= 0.f && r < 1.f, "tg_env_set_point_radius: bad argument");
+  env->r_pt = r;
+  return TG_OK;
+}
+
+extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stream_) {
+  TG_CHECK_ARG(env != nullptr, "tg_env_build: env is NULL");
+  TG_CHECK_ARG(n >= 0 && (n == 0 || xyz != nullptr), "tg_env_build: bad cloud");
+  if (n > env->max_points) {
+    tg_set_error("tg_env_build: %lld points exceed the env capacity %lld", (long long)n, (long long)env->max_points);
+    return TG_E_CAPACITY;
+  }
+  cudaStream_t st = (cudaStream_t)stream_;
+  TG_CUDA(cudaSetDevice(env->device));
+  TgGrid g;
+  memset(&g, 0, sizeof(g));
+  g.r_pt = env->r_pt;
+  float lo[3], hi[3];
+  bool have_box = false;
+  if (n > 0) {
+    if (env->fixed_bounds) {
+      memcpy(lo, env->lo, sizeof(lo));
+      memcpy(hi, env->hi, sizeof(hi));
+      have_box = true;
+    } else {
+      k_bounds_init<<<1, 32, 0, st>>>(env->bounds_dev);
+      k_bounds<<<min(tg_div_up(n, 256), 4 * env->sm_count), 256, 0, st>>>(xyz, (int)n, env->bounds_dev);
+      TG_CUDA(cudaMemcpyAsync(env->bounds_host, env->bounds_dev, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
+      TG_CUDA(cudaStreamSynchronize(st));
+      env->launches += 2;
+      if (env->bounds_host[0] <= env->bounds_host[3]) {  // at least one finite point
+        for (int a = 0; a < 3; ++a) {
+          lo[a] = ord2f(env->bounds_host[a]);
+          hi[a] = ord2f(env->bounds_host[3 + a]);
+        }
+        have_box = true;
+      }
+    }
+  }
+  if (!have_box) {  // empty world: every configuration is free of the cloud
+    g.empty = 1;
+    env->grid = g;
+    memset(&env->thr, 0, sizeof(env->thr));
+    TgHeader* h = env->header_host;
+    memset(h, 0, sizeof(TgHeader));
+    h->magic = 0x54594752495442ull;
+    h->bytes = TG_HEADER_BYTES;
+    h->grid = g;
+    TG_CUDA(cudaMemcpyAsync(env->blob, h, sizeof(TgHeader), cudaMemcpyHostToDevice, st));
+    return TG_OK;
+  }
+  if (!tg_plan_grids(env, lo, hi, &g)) {
+    tg_set_error("tg_env_build: cloud box [%g,%g,%g]-[%g,%g,%g] does not fit the grid capacity", lo[0], lo[1], lo[2],
+                 hi[0], hi[1], hi[2]);
+    return TG_E_CAPACITY;
+  }
+  g.n_points = (int)n;
+  TgHeader* h = env->header_host;
+  memset(h, 0, sizeof(TgHeader));
+  h->magic = 0x54594752495442ull;
+  tg_layout(env, &g, h);
+  if (h->bytes > env->blob_capacity) {
+    tg_set_error("tg_env_build: structure needs %zu bytes, capacity %zu", (size_t)h->bytes, env->blob_capacity);
+    return TG_E_CAPACITY;
+  }
+  const size_t nvox = (size_t)g.nx * g.ny * g.nz;
+  const int ncell = g.cnx * g.cny * g.cnz;
+  uint8_t* df = env->blob + h->off_df;
+  uint32_t* cell_start = (uint32_t*)(env->blob + h->off_cells);
+  float4* pts = (float4*)(env->blob + h->off_pts);
+
+  TG_CUDA(cudaMemsetAsync(df, 0, nvox, st));  // df doubles as the occupancy map until pass X has read it
+  TG_CUDA(cudaMemsetAsync(env->cell_count, 0, 4 * ((size_t)ncell + 1), st));
+  TG_CUDA(cudaMemsetAsync(env->bounds_dev + 6, 0, sizeof(int), st));
+  k_count<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, g, df, env->cell_count, env->key, env->rank, env->bounds_dev + 6);
+  const int nb = tg_div_up(ncell, SCAN_ITEMS);
+  k_scan_block_sums<<<nb, 256, 0, st>>>(env->cell_count, ncell, env->scan_tmp);
+  k_scan_sums<<<1, 1024, 0, st>>>(env->scan_tmp, nb);
+  k_scan_apply<<<nb, 256, 0, st>>>(env->cell_count, ncell, env->scan_tmp, cell_start);
+  k_scatter<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, env->key, env->rank, cell_start, pts);
+  const int rows = g.ny * g.nz;
+  k_edt_x<<<tg_div_up(rows, 8), 256, 8 * g.nx, st>>>(df, env->g1, g.nx, rows, g.window);
+  k_edt_y<<<dim3(tg_div_up(g.nx, 32), g.nz), 256, g.ny * 32, st>>>(env->g1, env->g2, g.nx, g.ny, g.window);
+  k_edt_z<<<dim3(tg_div_up(g.nx, 32), g.ny), 256, g.nz * 32 * 2, st>>>(env->g2, df, g.nx, g.ny, g.nz, g.window);
+  TG_CUDA(cudaGetLastError());
+  env->launches += 8;
+
+  tg_compute_thresholds(g, &env->thr);
+  env->grid = g;
+  h->grid = g;
+  h->thr = env->thr;
+  TG_CUDA(cudaMemcpyAsync(env->blob, h, sizeof(TgHeader), cudaMemcpyHostToDevice, st));
+  return TG_OK;
+}
+
+extern "C" int tg_env_build_host(tg_env* env, const float* xyz, int64_t n, void* stream_) {
+  TG_CHECK_ARG(env != nullptr, "tg_env_build_host: env is NULL");
+  TG_CHECK_ARG(n >= 0 && (n == 0 || xyz != nullptr), "tg_env_build_host: bad cloud");
+  if (n > env->max_points) {
+    tg_set_error("tg_env_build_host: %lld points exceed the env capacity %lld", (long long)n, (long long)env->max_points);
+    return TG_E_CAPACITY;
+  }
+  TG_CUDA(cudaSetDevice(env->device));
+  cudaStream_t st = (cudaStream_t)stream_;
+  if (n > 0) {
+    if (!env->xyz_stage) TG_CUDA(cudaMalloc(&env->xyz_stage, 12 * (size_t)env->max_points));
+    TG_CUDA(cudaMemcpyAsync(env->xyz_stage, xyz, 12 * (size_t)n, cudaMemcpyHostToDevice, st));
+  }
+  return tg_env_build(env, env->xyz_stage, n, stream_);
+}
+
+extern "C" int tg_env_stats(const tg_env* env, double* out8) {
+  TG_CHECK_ARG(env != nullptr && out8 != nullptr, "tg_env_stats: bad argument");
+  const TgGrid& g = env->grid;
+  out8[0] = g.n_points;
+  out8[1] = 0;  // filled by tg_env_counters-style readback below if available
+  out8[2] = g.nx; out8[3] = g.ny; out8[4] = g.nz;
+  out8[5] = (double)g.cnx * g.cny * g.cnz;
+  out8[6] = g.vpm;
+  out8[7] = g.slack;
+  if (!g.empty) {
+    int dropped = 0;
+    if (cudaMemcpy(&dropped, env->bounds_dev + 6, sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess) out8[1] = dropped;
+  }
+  return TG_OK;
+}
+
+extern "C" size_t tg_env_blob_capacity(const tg_env* env) { return env ? env->blob_capacity : 0; }
+
+extern "C" int tg_env_blob_ptr(tg_env* env, void** blob) {
+  TG_CHECK_ARG(env != nullptr && blob != nullptr, "tg_env_blob_ptr: bad argument");
+  *blob = env->blob;
+  return TG_OK;
+}
+
+extern "C" int tg_env_export(tg_env* env, void** blob, size_t* bytes) {
+  TG_CHECK_ARG(env != nullptr && blob != nullptr && bytes != nullptr, "tg_env_export: bad argument");
+  *blob = env->blob;
+  *bytes = (size_t)env->header_host->bytes;
+  if (*bytes == 0) {
+    tg_set_error("tg_env_export: nothing built yet");
+    return TG_E_STATE;
+  }
+  return TG_OK;
+}
+
+extern "C" int tg_env_import(tg_env* env, const void* blob, size_t bytes, void* stream_) {
+  TG_CHECK_ARG(env != nullptr && blob != nullptr && bytes >= TG_HEADER_BYTES, "tg_env_import: bad argument");
+  if (bytes > env->blob_capacity) {
+    tg_set_error("tg_env_import: blob of %zu bytes exceeds capacity %zu", bytes, env->blob_capacity);
+    return TG_E_CAPACITY;
+  }
+  cudaStream_t st = (cudaStream_t)stream_;
+  TG_CUDA(cudaSetDevice(env->device));
+  if (blob != env->blob) TG_CUDA(cudaMemcpyAsync(env->blob, blob, bytes, cudaMemcpyDeviceToDevice, st));
+  TG_CUDA(cudaMemcpyAsync(env->header_host, env->blob, sizeof(TgHeader), cudaMemcpyDeviceToHost, st));
+  TG_CUDA(cudaStreamSynchronize(st));
+  TgHeader* h = env->header_host;
+  if (h->magic != 0x54594752495442ull || h->bytes > bytes) {
+    tg_set_error("tg_env_import: not a tygrit_b200 structure blob");
+    return TG_E_ARG;
+  }
+  TgGrid g = h->grid;
+  if (!g.empty) {
+    g.df = env->blob + h->off_df;
+    g.cell_start = (const uint32_t*)(env->blob + h->off_cells);
+    g.pts = (const float4*)(env->blob + h->off_pts);
+  }
+  env->grid = g;
+  env->thr = h->thr;
+  env->r_pt = g.r_pt;
+  return TG_OK;
+}
+
+extern "C" int tg_env_set_obstacles(tg_env* env, const float* xyzr, int n, void* stream_) {
+  TG_CHECK_ARG(env != nullptr && n >= 0 && n <= TG_MAX_OBSTACLES && (n == 0 || xyzr), "tg_env_set_obstacles: bad argument (max 64 spheres)");
+  env->extras.n_obs = n;
+  for (int i = 0; i < n; ++i) env->extras.obs[i] = make_float4(xyzr[4 * i], xyzr[4 * i + 1], xyzr[4 * i + 2], xyzr[4 * i + 3]);
+  TG_CUDA(cudaSetDevice(env->device));
+  TG_CUDA(cudaMemcpyAsync(env->extras_dev, &env->extras, sizeof(TgExtras), cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+  TG_CUDA(cudaStreamSynchronize((cudaStream_t)stream_));
+  return TG_OK;
+}
+
+extern "C" int tg_env_set_attachment(tg_env* env, const float* xyzr, int n, const float* pos, const float* quat, void* stream_) {
+  TG_CHECK_ARG(env != nullptr && n >= 0 && n <= TG_MAX_ATTACHED && (n == 0 || xyzr), "tg_env_set_attachment: bad argument (max 64 spheres)");
+  double R[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, t[3] = {0, 0, 0};
+  if (pos) for (int a = 0; a < 3; ++a) t[a] = pos[a];
+  if (quat) {
+    double x = quat[0], y = quat[1], z = quat[2], w = quat[3];
+    const double nn = sqrt(x * x + y * y + z * z + w * w);
+    TG_CHECK_ARG(nn > 0, "tg_env_set_attachment: zero quaternion");
+    x /= nn; y /= nn; z /= nn; w /= nn;
+    R[0] = 1 - 2 * (y * y + z * z); R[1] = 2 * (x * y - z * w); R[2] = 2 * (x * z + y * w);
+    R[3] = 2 * (x * y + z * w); R[4] = 1 - 2 * (x * x + z * z); R[5] = 2 * (y * z - x * w);
+    R[6] = 2 * (x * z - y * w); R[7] = 2 * (y * z + x * w); R[8] = 1 - 2 * (x * x + y * y);
+  }
+  env->extras.n_att = n;
+  for (int i = 0; i < n; ++i) {
+    const double px = xyzr[4 * i], py = xyzr[4 * i + 1], pz = xyzr[4 * i + 2];
+    env->extras.att[i] = make_float4((float)(R[0] * px + R[1] * py + R[2] * pz + t[0]), (float)(R[3] * px + R[4] * py + R[5] * pz + t[1]),
+                                     (float)(R[6] * px + R[7] * py + R[8] * pz + t[2]), xyzr[4 * i + 3]);
+  }
+  TG_CUDA(cudaSetDevice(env->device));
+  TG_CUDA(cudaMemcpyAsync(env->extras_dev, &env->extras, sizeof(TgExtras), cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+  TG_CUDA(cudaStreamSynchronize((cudaStream_t)stream_));
+  return TG_OK;
+}

@@ -1,0 +1,225 @@
+// filter.cu — K4: robot self-filter (points inside the robot's collision volume are masked out).
+//
+// Reference: TyGrit/kinematics/robot_filter.py:13-64 (uniform radius for all 111 spheres, strict
+// `d2 < r2` removes, centres cast to f32 before the test) and the depth back-projection of
+// TyGrit/utils/depth.py:13-84.  HBM-bound: 4 B depth in + 1 B mask out per (state, pixel); the 111
+// centres of a state live in shared memory and a bounding box rejects non-robot pixels early.
+//
+// The inner test is written with explicit round-to-nearest mul/add (no FMA contraction) in the
+// order ((dx*dx + dy*dy) + dz*dz), which is what numpy evaluates; given identical f32 centres the
+// mask is bit-identical to the reference, not just equal outside a tolerance band.
+#include <math.h>
+
+#include "fk.cuh"
+
+#define TGF_BLOCK 256
+#define TGF_MAX_CENTRES 1024
+
+struct TgFilterState {  // per robot state, produced by k_filter_prepare
+  float cam_r[9];       // cam2world rotation (OpenCV camera axes -> world)
+  float cam_t[3];
+  float lo[3], hi[3];   // bounding box of the sphere centres
+  float c[TGM_N_SPHERES * 3];
+};
+
+__device__ __forceinline__ bool tg_inside_any(const float* __restrict__ c, int S, float px, float py, float pz, float r2) {
+  bool inside = false;
+  for (int s = 0; s < S; ++s) {
+    const float dx = __fsub_rn(px, c[3 * s]), dy = __fsub_rn(py, c[3 * s + 1]), dz = __fsub_rn(pz, c[3 * s + 2]);
+    const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+    inside |= d2 < r2;
+  }
+  return inside;
+}
+
+// ---- generic points x centres ---------------------------------------------------------------
+__global__ void __launch_bounds__(TGF_BLOCK)
+k_filter_points(const float* __restrict__ pts, int N, const float* __restrict__ centres, int S, float r2, float r,
+                uint8_t* __restrict__ keep) {
+  __shared__ float sc[TGF_MAX_CENTRES * 3];
+  __shared__ float sbox[6];
+  for (int j = threadIdx.x; j < 3 * S; j += TGF_BLOCK) sc[j] = centres[j];
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    float lo = INFINITY, hi = -INFINITY;
+    for (int s = 0; s < S; ++s) {
+      lo = fminf(lo, sc[3 * s + threadIdx.x]);
+      hi = fmaxf(hi, sc[3 * s + threadIdx.x]);
+    }
+    sbox[threadIdx.x] = lo - r - 1e-3f;
+    sbox[3 + threadIdx.x] = hi + r + 1e-3f;
+  }
+  __syncthreads();
+  for (int i = blockIdx.x * TGF_BLOCK + threadIdx.x; i < N; i += gridDim.x * TGF_BLOCK) {
+    const float px = pts[3 * (size_t)i], py = pts[3 * (size_t)i + 1], pz = pts[3 * (size_t)i + 2];
+    bool inside = false;
+    if (px >= sbox[0] && px <= sbox[3] && py >= sbox[1] && py <= sbox[4] && pz >= sbox[2] && pz <= sbox[5])
+      inside = tg_inside_any(sc, S, px, py, pz, r2);
+    keep[i] = inside ? 0 : 1;
+  }
+}
+
+extern "C" int tg_filter_points(const float* points, int64_t N, const float* centres, int S, float radius, uint8_t* keep,
+                                void* stream) {
+  TG_CHECK_ARG(N >= 0 && N < (1ll << 31), "tg_filter_points: N out of range");
+  TG_CHECK_ARG(S >= 0 && S <= TGF_MAX_CENTRES, "tg_filter_points: at most 1024 centres");
+  TG_CHECK_ARG(N == 0 || (points && keep && (S == 0 || centres)), "tg_filter_points: NULL buffer");
+  if (N == 0) return TG_OK;
+  const float r2 = (float)((double)radius * (double)radius);  // python: r2 = r * r (f64), compared in f32
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int blocks = min(tg_div_up(N, TGF_BLOCK), sms * 8);
+  k_filter_points<<<blocks, TGF_BLOCK, 0, (cudaStream_t)stream>>>(points, (int)N, centres, S, r2, radius, keep);
+  TG_CUDA(cudaGetLastError());
+  return TG_OK;
+}
+
+// ---- batched depth self-filter --------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_filter_prepare(const float* __restrict__ states, int S, float radius, TgFilterState* __restrict__ out) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= S) return;
+  const float* st = states + 13 * (size_t)s;
+  float q[10];
+#pragma unroll
+  for (int k = 0; k < 10; ++k) q[k] = st[3 + k];
+  TgFrame L[TGM_N_LINKS];
+  tg_fk_links(q, L);
+  const TgBase b = tg_base(st[0], st[1], st[2]);
+  TgFilterState& o = out[s];
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int j = 0; j < TGM_N_SPHERES; ++j) {
+    const float4 l = TGM_SPH_REF[j];
+    const float3 pb = tg_frame_apply(L[TGM_SPH_LINK[j]], l.x, l.y, l.z);
+    const float3 pw = tg_to_world(b, pb.x, pb.y, pb.z);
+    o.c[3 * j] = pw.x; o.c[3 * j + 1] = pw.y; o.c[3 * j + 2] = pw.z;
+    lo[0] = fminf(lo[0], pw.x); hi[0] = fmaxf(hi[0], pw.x);
+    lo[1] = fminf(lo[1], pw.y); hi[1] = fmaxf(hi[1], pw.y);
+    lo[2] = fminf(lo[2], pw.z); hi[2] = fmaxf(hi[2], pw.z);
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    o.lo[a] = lo[a] - radius - 1e-3f;
+    o.hi[a] = hi[a] + radius + 1e-3f;
+  }
+  // cam2world = SE2(base) * T(head_tilt) * Trans(cam offset) * R_cv->link   (camera.py:25-58)
+  const TgFrame& Tt = L[TGM_HEAD_TILT_LINK];
+  const float3 cb = tg_frame_apply(Tt, TGM_HEAD_CAMERA_OFF[0], TGM_HEAD_CAMERA_OFF[1], TGM_HEAD_CAMERA_OFF[2]);
+  const float3 cw = tg_to_world(b, cb.x, cb.y, cb.z);
+  o.cam_t[0] = cw.x; o.cam_t[1] = cw.y; o.cam_t[2] = cw.z;
+  // world rotation of head_tilt: Rz(theta) * R ; then columns: cv x -> -link y, cv y -> -link z, cv z -> link x
+  float Rw[9];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    Rw[c] = fmaf(b.c, Tt.r[c], -b.s * Tt.r[3 + c]);
+    Rw[3 + c] = fmaf(b.s, Tt.r[c], b.c * Tt.r[3 + c]);
+    Rw[6 + c] = Tt.r[6 + c];
+  }
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    o.cam_r[3 * r + 0] = -Rw[3 * r + 1];
+    o.cam_r[3 * r + 1] = -Rw[3 * r + 2];
+    o.cam_r[3 * r + 2] = Rw[3 * r + 0];
+  }
+}
+
+struct TgDepthParams {
+  int H, W, stride, Hs, Ws;
+  double fx, fy, cx, cy;  // intrinsics of the decimated image (K rows 0,1 divided by stride in f64)
+  float zmin, zmax, r2;
+};
+
+// one thread = PIX consecutive decimated pixels of one state
+template <int PIX>
+__global__ void __launch_bounds__(TGF_BLOCK)
+k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __restrict__ prep, TgDepthParams p,
+                    uint8_t* __restrict__ mask, float* __restrict__ world) {
+  __shared__ TgFilterState st;
+  const int s = blockIdx.y;
+  {
+    const float* src = reinterpret_cast<const float*>(prep + s);
+    float* dst = reinterpret_cast<float*>(&st);
+    for (int j = threadIdx.x; j < (int)(sizeof(TgFilterState) / 4); j += TGF_BLOCK) dst[j] = src[j];
+  }
+  __syncthreads();
+  const int npx = p.Hs * p.Ws;
+  const int first = (blockIdx.x * TGF_BLOCK + threadIdx.x) * PIX;
+  if (first >= npx) return;
+  const float* img = depth + (size_t)s * p.H * p.W;
+  float d[PIX];
+  if (PIX == 4 && p.stride == 1 && (p.W & 3) == 0) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(img + first));
+    d[0] = v.x; d[1 % PIX] = v.y; d[2 % PIX] = v.z; d[3 % PIX] = v.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < PIX; ++k) {
+      const int pix = first + k;
+      if (pix < npx) {
+        const int v = pix / p.Ws, u = pix - v * p.Ws;
+        d[k] = __ldg(img + (size_t)(v * p.stride) * p.W + u * p.stride);
+      } else d[k] = 0.f;
+    }
+  }
+  uint8_t out[PIX];
+#pragma unroll
+  for (int k = 0; k < PIX; ++k) {
+    const int pix = first + k;
+    const int v = pix / p.Ws, u = pix - v * p.Ws;
+    float z = d[k];
+    if (isnan(z)) z = 0.f;                       // np.nan_to_num
+    else if (isinf(z)) z = z > 0 ? 3.4028234663852886e38f : -3.4028234663852886e38f;
+    bool ok = pix < npx && z > 0.f && z >= p.zmin && z <= p.zmax;
+    float wx = 0.f, wy = 0.f, wz = 0.f;
+    if (ok) {
+      // depth.py:41-46 evaluated as numpy 2 does: (f32 index - f64 c) * f32 depth / f64 f, rounded once
+      const float xc = (float)((((double)(float)u - p.cx) * (double)z) / p.fx);
+      const float yc = (float)((((double)(float)v - p.cy) * (double)z) / p.fy);
+      // depth.py:79-83: p_w = p_c @ R^T + t in f32
+      wx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[0]), __fmul_rn(yc, st.cam_r[1])), __fmul_rn(z, st.cam_r[2])), st.cam_t[0]);
+      wy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[3]), __fmul_rn(yc, st.cam_r[4])), __fmul_rn(z, st.cam_r[5])), st.cam_t[1]);
+      wz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[6]), __fmul_rn(yc, st.cam_r[7])), __fmul_rn(z, st.cam_r[8])), st.cam_t[2]);
+      if (wx >= st.lo[0] && wx <= st.hi[0] && wy >= st.lo[1] && wy <= st.hi[1] && wz >= st.lo[2] && wz <= st.hi[2])
+        ok = !tg_inside_any(st.c, TGM_N_SPHERES, wx, wy, wz, p.r2);
+    }
+    out[k] = ok ? 1 : 0;
+    if (world != nullptr && pix < npx) {
+      float* w = world + ((size_t)s * npx + pix) * 3;
+      w[0] = wx; w[1] = wy; w[2] = wz;
+    }
+  }
+  uint8_t* m = mask + (size_t)s * npx + first;
+  if (PIX == 4 && first + 3 < npx && ((((size_t)s * npx + first) & 3) == 0)) {
+    *reinterpret_cast<uint32_t*>(m) = (uint32_t)out[0] | ((uint32_t)out[1 % PIX] << 8) | ((uint32_t)out[2 % PIX] << 16) | ((uint32_t)out[3 % PIX] << 24);
+  } else {
+#pragma unroll
+    for (int k = 0; k < PIX; ++k)
+      if (first + k < npx) m[k] = out[k];
+  }
+}
+
+extern "C" int tg_self_filter_depth(const float* depth, int H, int W, int stride, const double* K, const float* states, int64_t S,
+                                    float radius, float zmin, float zmax, uint8_t* mask, float* world, void* stream_) {
+  TG_CHECK_ARG(H > 0 && W > 0 && stride >= 1 && S >= 0 && S < 65536, "tg_self_filter_depth: bad shape (S < 65536)");
+  TG_CHECK_ARG(S == 0 || (depth && K && states && mask), "tg_self_filter_depth: NULL buffer");
+  TG_CHECK_ARG(((uintptr_t)depth & 15) == 0, "tg_self_filter_depth: depth must be 16-byte aligned");
+  if (S == 0) return TG_OK;
+  cudaStream_t st = (cudaStream_t)stream_;
+  TgDepthParams p;
+  p.H = H; p.W = W; p.stride = stride;
+  p.Hs = (H + stride - 1) / stride;
+  p.Ws = (W + stride - 1) / stride;
+  p.fx = K[0] / stride; p.cx = K[2] / stride;  // depth.py:32-36: K[0,:] /= stride ; K[1,:] /= stride
+  p.fy = K[4] / stride; p.cy = K[5] / stride;
+  if (stride == 1) { p.fx = K[0]; p.cx = K[2]; p.fy = K[4]; p.cy = K[5]; }
+  p.zmin = zmin; p.zmax = zmax;
+  p.r2 = (float)((double)radius * (double)radius);
+  TgFilterState* prep = nullptr;
+  TG_CUDA(cudaMallocAsync(&prep, sizeof(TgFilterState) * (size_t)S, st));
+  k_filter_prepare<<<tg_div_up(S, 128), 128, 0, st>>>(states, (int)S, radius, prep);
+  const int npx = p.Hs * p.Ws;
+  dim3 grid(tg_div_up(npx, TGF_BLOCK * 4), (unsigned)S);
+  k_self_filter_depth<4><<<grid, TGF_BLOCK, 0, st>>>(depth, prep, p, mask, world);
+  TG_CUDA(cudaGetLastError());
+  TG_CUDA(cudaFreeAsync(prep, st));
+  return TG_OK;
+}

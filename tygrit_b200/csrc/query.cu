@@ -1,0 +1,341 @@
+// query.cu — kernels and C entry points for configuration and motion-edge verdicts.
+//
+// tg_check_configs replaces a batch of VampPreviewPlanner.validate_config calls
+// (TyGrit/planning/fetch/vamp_preview.py:159-163 -> :328-338 validate_whole_body_config);
+// tg_check_edges replaces VAMP's validate_motion as used by the planners and by
+// check_trajectory_collisions (planning/fetch/algorithms.py:37,51; vamp_preview.py:306-322).
+//
+// Launch shape: phase 1 is one lane per configuration (a warp = a batch of 32 configurations,
+// 128-bit loads of the joint vector), grid sized in waves of the SM count; ambiguous
+// configurations are appended to a queue with one warp-aggregated atomic; phase 2 drains the
+// queue with one lane per item over the sorted cell rows.
+#include <math.h>
+#include <string.h>
+
+#include <vector>
+
+#include "query.cuh"
+
+#define TG_BLOCK 128
+
+__device__ __forceinline__ void tg_push_item(const TgGrid& g, TgQueue qu, TgCounters* ctr, bool need, uint32_t target,
+                                             const uint32_t* amb, const float* cfg, uint8_t* valid) {
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned m = __ballot_sync(__activemask(), need);
+  if (!need) return;
+  const unsigned leader = __ffs(m) - 1;
+  unsigned base = 0;
+  if (lane == leader) base = atomicAdd(qu.count, (unsigned)__popc(m));
+  base = __shfl_sync(m, base, leader);
+  const unsigned slot = base + __popc(m & ((1u << lane) - 1u));
+  if (slot < qu.capacity) {
+    TgItem it;
+    it.target = target;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) it.mask[w] = amb[w];
+#pragma unroll
+    for (int i = 0; i < 11; ++i) it.cfg[i] = cfg[i];
+    float4* dst = reinterpret_cast<float4*>(qu.items + slot);
+    const float4* src = reinterpret_cast<const float4*>(&it);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = src[i];
+  } else {  // queue full: resolve right here (slow, rare, still exact)
+    atomicAdd(&ctr->overflow_inline, 1ull);
+    if (tg_resolve_item(g, cfg, amb, nullptr)) valid[target] = 0;
+  }
+}
+
+__global__ void __launch_bounds__(TG_BLOCK)
+k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm,
+                const float* __restrict__ base, int B, uint8_t* __restrict__ valid, TgQueue qu, TgCounters* ctr) {
+  const int i = blockIdx.x * TG_BLOCK + threadIdx.x;
+  const bool live = i < B;
+  float cfg[11];
+  if (live) {
+    const float4 a0 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i);
+    const float4 a1 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i + 1);
+    cfg[0] = __ldg(base + 3 * (size_t)i); cfg[1] = __ldg(base + 3 * (size_t)i + 1); cfg[2] = __ldg(base + 3 * (size_t)i + 2);
+    cfg[3] = a0.x; cfg[4] = a0.y; cfg[5] = a0.z; cfg[6] = a0.w;
+    cfg[7] = a1.x; cfg[8] = a1.y; cfg[9] = a1.z; cfg[10] = a1.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 11; ++k) cfg[k] = 0.f;
+  }
+  TgClass cl;
+  cl.collide = false;
+  cl.amb[0] = cl.amb[1] = cl.amb[2] = cl.amb[3] = 0u;
+  if (live && !g.empty) tg_classify(g, thr, cfg + 3, cfg[0], cfg[1], cfg[2], cl);
+  if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
+  if (live) valid[i] = cl.collide ? 0 : 1;
+  const bool need = live && !cl.collide && (cl.amb[0] | cl.amb[1] | cl.amb[2] | cl.amb[3]) != 0u;
+  const unsigned ncol = __popc(__ballot_sync(0xffffffffu, live && cl.collide));
+  if ((threadIdx.x & 31) == 0 && ncol) atomicAdd(&ctr->definite_collisions, (unsigned long long)ncol);
+  tg_push_item(g, qu, ctr, need, (uint32_t)i, cl.amb, cfg, valid);
+}
+
+__global__ void __launch_bounds__(TG_BLOCK) k_resolve(const TgGrid g, TgQueue qu, uint8_t* __restrict__ valid, TgCounters* ctr) {
+  const unsigned n = min(*qu.count, qu.capacity);
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->items, (unsigned long long)n);
+  for (unsigned i = blockIdx.x * TG_BLOCK + threadIdx.x; i < n; i += gridDim.x * TG_BLOCK) {
+    TgItem it;
+    const float4* src = reinterpret_cast<const float4*>(qu.items + i);
+    float4* dst = reinterpret_cast<float4*>(&it);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) dst[k] = src[k];
+    if (valid[it.target] == 0) continue;  // edge already refuted by another sample
+    if (tg_resolve_item(g, it.cfg, it.mask, nullptr)) valid[it.target] = 0;
+  }
+}
+
+// One warp per edge.  Round j tests samples k = lane * rounds + j + 1 (k <= rake n): every round is
+// a uniform sweep over the whole segment, so a colliding edge is usually refuted in the first round
+// and the warp leaves through __any_sync.
+__global__ void __launch_bounds__(TG_BLOCK)
+k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm0,
+              const float* __restrict__ base0, const float* __restrict__ arm1, const float* __restrict__ base1, int E, int rake,
+              float resolution, uint8_t* __restrict__ valid, unsigned long long* __restrict__ n_checks, TgQueue qu,
+              TgCounters* ctr) {
+  const unsigned lane = threadIdx.x & 31;
+  const int warps_per_grid = gridDim.x * (TG_BLOCK / 32);
+  unsigned long long my_checks = 0;
+  for (int e = blockIdx.x * (TG_BLOCK / 32) + (threadIdx.x >> 5); e < E; e += warps_per_grid) {
+    float a[11], d[11];
+    a[0] = __ldg(base0 + 3 * (size_t)e); a[1] = __ldg(base0 + 3 * (size_t)e + 1); a[2] = __ldg(base0 + 3 * (size_t)e + 2);
+    d[0] = __ldg(base1 + 3 * (size_t)e); d[1] = __ldg(base1 + 3 * (size_t)e + 1); d[2] = __ldg(base1 + 3 * (size_t)e + 2);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      a[3 + k] = __ldg(arm0 + 8 * (size_t)e + k);
+      d[3 + k] = __ldg(arm1 + 8 * (size_t)e + k);
+    }
+    double s2 = 0.0;  // |b - a|^2 in fp64, order x, y, theta, q0..q7 (matches oracle/collide.py edge_n)
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+      const double dk = (double)d[k] - (double)a[k];
+      s2 = s2 + dk * dk;
+      d[k] = d[k] - a[k];
+    }
+    const double nn = ceil(sqrt(s2) * ((double)resolution / (double)rake));
+    const int n = nn < 1.0 ? 1 : (nn > 1.0e6 ? 1000000 : (int)nn);
+    const int total = rake * n;
+    const int rounds = (total + 31) >> 5;
+    if (lane == 0) my_checks += (unsigned long long)total;
+    bool hit = false;
+    const float inv_total = 1.0f / (float)total;
+    if (lane == 0) valid[e] = 1;  // provisional; cleared below, by an inline resolve, or by phase 2
+    __syncwarp();
+    for (int j = 0; j < rounds && !hit; ++j) {
+      const int k = (int)lane * rounds + j + 1;
+      const bool live = k <= total;
+      float cfg[11];
+      const float t = (float)k * inv_total;
+#pragma unroll
+      for (int c = 0; c < 11; ++c) cfg[c] = fmaf(t, d[c], a[c]);
+      TgClass cl;
+      cl.collide = false;
+      cl.amb[0] = cl.amb[1] = cl.amb[2] = cl.amb[3] = 0u;
+      if (live && !g.empty) tg_classify(g, thr, cfg + 3, cfg[0], cfg[1], cfg[2], cl);
+      if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
+      hit = __any_sync(0xffffffffu, live && cl.collide);
+      if (!hit) {
+        const bool need = live && (cl.amb[0] | cl.amb[1] | cl.amb[2] | cl.amb[3]) != 0u;
+        tg_push_item(g, qu, ctr, need, (uint32_t)e, cl.amb, cfg, valid);
+      }
+    }
+    __syncwarp();
+    if (lane == 0 && hit) {
+      valid[e] = 0;
+      atomicAdd(&ctr->definite_collisions, 1ull);
+    }
+    __syncwarp();
+  }
+  if (n_checks != nullptr && lane == 0 && my_checks) atomicAdd(n_checks, my_checks);
+}
+
+// clearance (optional output of tg_check_configs): exact, clipped at TG_CLEARANCE_CAP
+__global__ void __launch_bounds__(TG_BLOCK)
+k_clearance(const TgGrid g, const TgExtras* __restrict__ ex, const float* __restrict__ arm, const float* __restrict__ base,
+            int B, float* __restrict__ clearance) {
+  const int i = blockIdx.x * TG_BLOCK + threadIdx.x;
+  if (i >= B) return;
+  float q10[10];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) q10[k] = arm[8 * (size_t)i + k];
+  q10[8] = q10[9] = 0.f;
+  TgFrame L[TGM_N_LINKS];
+  tg_fk_links(q10, L);
+  const TgBase b = tg_base(base[3 * (size_t)i], base[3 * (size_t)i + 1], base[3 * (size_t)i + 2]);
+  float best = TG_CLEARANCE_CAP;
+  const int n_att = ex ? ex->n_att : 0, n_obs = ex ? ex->n_obs : 0;
+  for (int k = 0; k < TG_N_SPHERES + n_att; ++k) {
+    float4 c;
+    if (k < TG_N_SPHERES) c = tg_sphere_world(L, b, k);
+    else {
+      const float4 l = ex->att[k - TG_N_SPHERES];
+      const float3 pb = tg_frame_apply(L[TGM_GRIPPER_LINK], l.x, l.y, l.z);
+      const float3 pw = tg_to_world(b, pb.x, pb.y, pb.z);
+      c = make_float4(pw.x, pw.y, pw.z, l.w);
+    }
+    if (!g.empty) {
+      const float R = c.w + g.r_pt;
+      // lower bound from the grid: skip spheres that cannot improve the running minimum
+      const int code = tg_probe(g, c.x * g.vpm, c.y * g.vpm, c.z * g.vpm);
+      const float dlo = (float)code * g.q - g.slack - R;
+      if (dlo < best) best = fminf(best, tg_sphere_clearance(g, c.x, c.y, c.z, R, fmaxf(best, 0.f)));
+    }
+    for (int o = 0; o < n_obs; ++o) {
+      const float4 ob = ex->obs[o];
+      const float dx = c.x - ob.x, dy = c.y - ob.y, dz = c.z - ob.z;
+      best = fminf(best, sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) - c.w - ob.w);
+    }
+  }
+  clearance[i] = best;
+}
+
+__global__ void k_fill_u8(uint8_t* p, int n, uint8_t v) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host entry points
+// ------------------------------------------------------------------------------------------------
+static inline const TgExtras* tg_extras_ptr(const tg_env* env) {
+  return (env->extras.n_obs > 0 || env->extras.n_att > 0) ? env->extras_dev : nullptr;
+}
+
+static inline TgQueue tg_queue_slot(const tg_env* env, int slot) {
+  const unsigned half = env->queue_capacity / 2;
+  return TgQueue{env->items + (size_t)slot * half, env->queue_count + 4 * slot, half};
+}
+
+int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int64_t B, uint8_t* valid, float* clearance,
+                          void* stream_, int slot) {
+  TG_CHECK_ARG(env != nullptr, "tg_check_configs: env is NULL");
+  TG_CHECK_ARG(B >= 0 && (B == 0 || (arm && base && valid)), "tg_check_configs: NULL buffer");
+  TG_CHECK_ARG(((uintptr_t)arm & 15) == 0, "tg_check_configs: arm must be 16-byte aligned");
+  if (B == 0) return TG_OK;
+  cudaStream_t st = (cudaStream_t)stream_;
+  TG_CUDA(cudaSetDevice(env->device));
+  const TgExtras* ex = tg_extras_ptr(env);
+  TgQueue qu = tg_queue_slot(env, slot);
+  const int64_t chunk = (int64_t)qu.capacity;  // at most one item per configuration: never overflows
+  for (int64_t off = 0; off < B; off += chunk) {
+    const int nb = (int)((B - off) < chunk ? (B - off) : chunk);
+    if (env->grid.empty && ex == nullptr) {
+      k_fill_u8<<<tg_div_up(nb, 256), 256, 0, st>>>(valid + off, nb, 1);
+      env->launches += 1;
+    } else {
+      TG_CUDA(cudaMemsetAsync(qu.count, 0, sizeof(unsigned), st));
+      cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+      if (env->timing) {
+        for (int k = 0; k < 3; ++k) TG_CUDA(cudaEventCreate(&ev[k]));
+        TG_CUDA(cudaEventRecord(ev[0], st));
+      }
+      k_check_configs<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(env->grid, env->thr, ex, arm + 8 * off, base + 3 * off, nb,
+                                                                   valid + off, qu, env->counters_dev);
+      if (env->timing) TG_CUDA(cudaEventRecord(ev[1], st));
+      if (!env->grid.empty) {
+        k_resolve<<<env->sm_count * 8, TG_BLOCK, 0, st>>>(env->grid, qu, valid + off, env->counters_dev);
+        env->launches += 1;
+      }
+      if (env->timing) {
+        TG_CUDA(cudaEventRecord(ev[2], st));
+        for (int k = 0; k < 3; ++k) env->timing_events->push_back(ev[k]);
+      }
+      env->launches += 1;
+    }
+    if (clearance) {
+      k_clearance<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(env->grid, ex, arm + 8 * off, base + 3 * off, nb, clearance + off);
+      env->launches += 1;
+    }
+  }
+  TG_CUDA(cudaGetLastError());
+  return TG_OK;
+}
+
+extern "C" int tg_check_configs(tg_env* env, const float* arm, const float* base, int64_t B, uint8_t* valid, float* clearance,
+                                void* stream_) {
+  return tg_check_configs_slot(env, arm, base, B, valid, clearance, stream_, 0);
+}
+
+int tg_check_edges_slot(tg_env* env, const float* arm0, const float* base0, const float* arm1, const float* base1, int64_t E,
+                        int rake, float resolution, uint8_t* valid, int64_t* n_checks, void* stream_, int slot) {
+  TG_CHECK_ARG(env != nullptr, "tg_check_edges: env is NULL");
+  TG_CHECK_ARG(E >= 0 && (E == 0 || (arm0 && base0 && arm1 && base1 && valid)), "tg_check_edges: NULL buffer");
+  TG_CHECK_ARG(rake >= 1 && rake <= 64 && resolution > 0.f, "tg_check_edges: rake must be in [1,64], resolution > 0");
+  cudaStream_t st = (cudaStream_t)stream_;
+  TG_CUDA(cudaSetDevice(env->device));
+  if (n_checks) TG_CUDA(cudaMemsetAsync(n_checks, 0, sizeof(int64_t), st));
+  if (E == 0) return TG_OK;
+  const TgExtras* ex = tg_extras_ptr(env);
+  TgQueue qu = tg_queue_slot(env, slot);
+  const int64_t chunk = 1 << 18;  // edges per launch pair: keeps the ambiguous queue well inside its capacity
+  for (int64_t off = 0; off < E; off += chunk) {
+    const int ne = (int)((E - off) < chunk ? (E - off) : chunk);
+    TG_CUDA(cudaMemsetAsync(qu.count, 0, sizeof(unsigned), st));
+    const int blocks = min(tg_div_up(ne, TG_BLOCK / 32), env->sm_count * 16);
+    k_check_edges<<<blocks, TG_BLOCK, 0, st>>>(env->grid, env->thr, ex, arm0 + 8 * off, base0 + 3 * off, arm1 + 8 * off,
+                                               base1 + 3 * off, ne, rake, resolution, valid + off,
+                                               (unsigned long long*)n_checks, qu, env->counters_dev);
+    env->launches += 1;
+    if (!env->grid.empty) {
+      k_resolve<<<env->sm_count * 8, TG_BLOCK, 0, st>>>(env->grid, qu, valid + off, env->counters_dev);
+      env->launches += 1;
+    }
+  }
+  TG_CUDA(cudaGetLastError());
+  return TG_OK;
+}
+
+extern "C" int tg_check_edges(tg_env* env, const float* arm0, const float* base0, const float* arm1, const float* base1,
+                              int64_t E, int rake, float resolution, uint8_t* valid, int64_t* n_checks, void* stream_) {
+  return tg_check_edges_slot(env, arm0, base0, arm1, base1, E, rake, resolution, valid, n_checks, stream_, 0);
+}
+
+// Device-time instrumentation: CUDA events around every phase-1 / phase-2 launch of tg_check_configs
+// (on the launching stream), so bench.py can report the dominant kernel's own duration.
+extern "C" int tg_env_set_timing(tg_env* env, int on) {
+  TG_CHECK_ARG(env != nullptr, "tg_env_set_timing: env is NULL");
+  env->timing = on ? 1 : 0;
+  if (!on) {
+    for (cudaEvent_t e : *env->timing_events) cudaEventDestroy(e);
+    env->timing_events->clear();
+  }
+  return TG_OK;
+}
+
+extern "C" int tg_env_timing_read(tg_env* env, double* out3) {
+  TG_CHECK_ARG(env != nullptr && out3 != nullptr, "tg_env_timing_read: bad argument");
+  TG_CUDA(cudaSetDevice(env->device));
+  double p1 = 0, p2 = 0;
+  std::vector<cudaEvent_t>& ev = *env->timing_events;
+  for (size_t i = 0; i + 2 < ev.size(); i += 3) {
+    TG_CUDA(cudaEventSynchronize(ev[i + 2]));
+    float a = 0, b = 0;
+    TG_CUDA(cudaEventElapsedTime(&a, ev[i], ev[i + 1]));
+    TG_CUDA(cudaEventElapsedTime(&b, ev[i + 1], ev[i + 2]));
+    p1 += a;
+    p2 += b;
+  }
+  out3[0] = p1;
+  out3[1] = p2;
+  out3[2] = (double)(ev.size() / 3);
+  for (cudaEvent_t e : ev) cudaEventDestroy(e);
+  ev.clear();
+  return TG_OK;
+}
+
+extern "C" int tg_env_counters(tg_env* env, int64_t* out4, void* stream_) {
+  TG_CHECK_ARG(env != nullptr && out4 != nullptr, "tg_env_counters: bad argument");
+  cudaStream_t st = (cudaStream_t)stream_;
+  TG_CUDA(cudaSetDevice(env->device));
+  TG_CUDA(cudaMemcpyAsync(env->counters_host, env->counters_dev, sizeof(TgCounters), cudaMemcpyDeviceToHost, st));
+  TG_CUDA(cudaMemsetAsync(env->counters_dev, 0, sizeof(TgCounters), st));
+  TG_CUDA(cudaStreamSynchronize(st));
+  out4[0] = (int64_t)env->counters_host->definite_collisions;
+  out4[1] = (int64_t)env->counters_host->items;
+  out4[2] = (int64_t)env->counters_host->overflow_inline;
+  out4[3] = env->launches;
+  env->launches = 0;
+  return TG_OK;
+}

@@ -42,6 +42,7 @@ def parse():
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--configs", type=int, default=64 * 1024 * 1024, help="configurations per GPU per step")
     p.add_argument("--cpu-sample", type=int, default=4_000_000, help="configurations per CPU-baseline sample")
+    p.add_argument("--vpm", type=float, default=50.0, help="distance-grid voxels per metre")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu", action="store_true")
     return p.parse_args()
@@ -127,7 +128,7 @@ def main():
     config = {
         "workload": f"C4: bulk check of {args.configs} random Fetch configs per GPU vs {CLOUD_POINTS}-point synthetic room cloud",
         "configs_per_gpu_per_step": args.configs, "cloud_points": CLOUD_POINTS, "point_radius": 0.03,
-        "voxels_per_metre": 50, "l2": "inputs (44 B/config = %.1f GB/step) are larger than L2" % (args.configs * 44 / 1e9),
+        "voxels_per_metre": args.vpm, "l2": "inputs (44 B/config = %.1f GB/step) are larger than L2" % (args.configs * 44 / 1e9),
         "parallelism": f"configs sharded over {world} rank(s), cloud structure broadcast",
     }
 
@@ -158,7 +159,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     # ---- world: rank 0 ingests the cloud and builds; the structure is broadcast ------------------
-    w = CollisionWorld(device=local, max_points=1 << 20)
+    w = CollisionWorld(device=local, max_points=1 << 20, voxels_per_metre=args.vpm, max_voxels=192 << 20)
     t_build = t_bcast = 0.0
     cloud = None
     if rank == 0:

@@ -157,11 +157,14 @@ struct tg_env {
   float* pin_clear[2];
   int64_t chunk;
   int sm_count;
+  int occ_configs, occ_resolve;  // resident blocks per SM of the persistent query kernels
 };
 
 int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int64_t B, uint8_t* valid, float* clearance,
                           void* stream, int slot);
 int tg_check_edges_slot(tg_env* env, const float* arm0, const float* base0, const float* arm1, const float* base1, int64_t E,
                         int rake, float resolution, uint8_t* valid, int64_t* n_checks, void* stream, int slot);
+
+int tg_query_occupancy(tg_env* env);
 
 static inline int tg_div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

@@ -407,6 +407,10 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
   cudaDeviceProp prop;
   TG_CUDA(cudaGetDeviceProperties(&prop, device));
   env->sm_count = prop.multiProcessorCount;
+  {
+    const int rc = tg_query_occupancy(env);
+    if (rc) return rc;
+  }
   // empty world until the first build
   env->grid.empty = 1;
   env->grid.r_pt = point_radius;

@@ -18,6 +18,9 @@
 
 #define TG_BLOCK 128
 
+// ------------------------------------------------------------------------------------------------
+// ambiguous-configuration queue (global): one 64-byte item per configuration with >= 1 ambiguous sphere
+// ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void tg_push_item(const TgGrid& g, TgQueue qu, TgCounters* ctr, bool need, uint32_t target,
                                              const uint32_t* amb, const float* cfg, uint8_t* valid) {
   const unsigned lane = threadIdx.x & 31;
@@ -41,55 +44,247 @@ __device__ __forceinline__ void tg_push_item(const TgGrid& g, TgQueue qu, TgCoun
     for (int i = 0; i < 4; ++i) dst[i] = src[i];
   } else {  // queue full: resolve right here (slow, rare, still exact)
     atomicAdd(&ctr->overflow_inline, 1ull);
-    if (tg_resolve_item(g, cfg, amb, nullptr)) valid[target] = 0;
+    if (tg_resolve_item(g, cfg, amb)) valid[target] = 0;
   }
 }
 
-__global__ void __launch_bounds__(TG_BLOCK)
-k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm,
-                const float* __restrict__ base, int B, uint8_t* __restrict__ valid, TgQueue qu, TgCounters* ctr) {
-  const int i = blockIdx.x * TG_BLOCK + threadIdx.x;
-  const bool live = i < B;
-  float cfg[11];
-  if (live) {
-    const float4 a0 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i);
-    const float4 a1 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i + 1);
-    cfg[0] = __ldg(base + 3 * (size_t)i); cfg[1] = __ldg(base + 3 * (size_t)i + 1); cfg[2] = __ldg(base + 3 * (size_t)i + 2);
-    cfg[3] = a0.x; cfg[4] = a0.y; cfg[5] = a0.z; cfg[6] = a0.w;
-    cfg[7] = a1.x; cfg[8] = a1.y; cfg[9] = a1.z; cfg[10] = a1.w;
-  } else {
-#pragma unroll
-    for (int k = 0; k < 11; ++k) cfg[k] = 0.f;
-  }
+// ------------------------------------------------------------------------------------------------
+// phase 1: configurations.  Persistent blocks; one lane = one configuration in both stages.
+// Stage A (20 base-pose spheres) refutes ~70 % of random configurations; the survivors are
+// compacted through a shared-memory ring so that stage B (91 spheres + the arm chain) always runs
+// with full warps.  Two block barriers per tile of TGC_BLOCK configurations.
+// ------------------------------------------------------------------------------------------------
+#define TGC_BLOCK 256
+#define TGC_RING 512  // >= 2 * TGC_BLOCK, power of two
+
+struct TgRing {
+  float cfg[11][TGC_RING];
+  uint32_t idx[TGC_RING];
+  uint32_t amb0[TGC_RING];
+};
+
+__device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& thr, const TgExtras* __restrict__ ex,
+                                                 const float* cfg, uint32_t idx, uint32_t amb0, uint8_t* __restrict__ valid,
+                                                 TgQueue qu, TgCounters* ctr, bool live) {
   TgClass cl;
-  cl.collide = false;
-  cl.amb[0] = cl.amb[1] = cl.amb[2] = cl.amb[3] = 0u;
-  if (live && !g.empty) tg_classify(g, thr, cfg + 3, cfg[0], cfg[1], cfg[2], cl);
-  if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
-  if (live) valid[i] = cl.collide ? 0 : 1;
-  const bool need = live && !cl.collide && (cl.amb[0] | cl.amb[1] | cl.amb[2] | cl.amb[3]) != 0u;
+  tg_class_clear(cl);
+  cl.amb[0] = amb0;
+  if (live) {
+    if (!g.empty) {
+      const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
+      tg_stage_b(g, thr, p, cfg + 3, cl);
+    }
+    if (!cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
+    valid[idx] = cl.collide ? 0 : 1;
+  }
   const unsigned ncol = __popc(__ballot_sync(0xffffffffu, live && cl.collide));
   if ((threadIdx.x & 31) == 0 && ncol) atomicAdd(&ctr->definite_collisions, (unsigned long long)ncol);
-  tg_push_item(g, qu, ctr, need, (uint32_t)i, cl.amb, cfg, valid);
+  const bool need = live && !cl.collide && (cl.amb[0] | cl.amb[1] | cl.amb[2] | cl.amb[3]) != 0u;
+  tg_push_item(g, qu, ctr, need, idx, cl.amb, cfg, valid);
 }
 
-__global__ void __launch_bounds__(TG_BLOCK) k_resolve(const TgGrid g, TgQueue qu, uint8_t* __restrict__ valid, TgCounters* ctr) {
-  const unsigned n = min(*qu.count, qu.capacity);
-  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->items, (unsigned long long)n);
-  for (unsigned i = blockIdx.x * TG_BLOCK + threadIdx.x; i < n; i += gridDim.x * TG_BLOCK) {
-    TgItem it;
-    const float4* src = reinterpret_cast<const float4*>(qu.items + i);
-    float4* dst = reinterpret_cast<float4*>(&it);
+__global__ void __launch_bounds__(TGC_BLOCK, 4)
+k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm,
+                const float* __restrict__ base, int B, uint8_t* __restrict__ valid, TgQueue qu, TgCounters* ctr) {
+  __shared__ TgRing ring;
+  __shared__ unsigned s_tail;
+  if (threadIdx.x == 0) s_tail = 0;
+  __syncthreads();
+  unsigned head = 0;  // ring positions count up; slot = position & (TGC_RING - 1)
+  const unsigned lane = threadIdx.x & 31;
+  const int ntiles = (B + TGC_BLOCK - 1) / TGC_BLOCK;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int i = tile * TGC_BLOCK + threadIdx.x;
+    const bool live = i < B;
+    float cfg[11];
+    TgClass cl;
+    tg_class_clear(cl);
+    if (live) {
+      cfg[0] = __ldg(base + 3 * (size_t)i); cfg[1] = __ldg(base + 3 * (size_t)i + 1); cfg[2] = __ldg(base + 3 * (size_t)i + 2);
+      if (!g.empty) {
+        const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
+        tg_stage_a(g, thr, p, cl);
+      }
+      if (cl.collide) valid[i] = 0;
+    }
+    const bool surv = live && !cl.collide;
+    const unsigned m = __ballot_sync(0xffffffffu, surv);
+    const unsigned ncol = __popc(__ballot_sync(0xffffffffu, live)) - __popc(m);
+    if (lane == 0 && ncol) atomicAdd(&ctr->definite_collisions, (unsigned long long)ncol);
+    if (m) {
+      unsigned pos = 0;
+      if (lane == 0) pos = atomicAdd(&s_tail, (unsigned)__popc(m));
+      pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
+      if (surv) {
+        const float4 a0 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i);
+        const float4 a1 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i + 1);
+        const unsigned sl = pos & (TGC_RING - 1);
+        ring.cfg[0][sl] = cfg[0]; ring.cfg[1][sl] = cfg[1]; ring.cfg[2][sl] = cfg[2];
+        ring.cfg[3][sl] = a0.x; ring.cfg[4][sl] = a0.y; ring.cfg[5][sl] = a0.z; ring.cfg[6][sl] = a0.w;
+        ring.cfg[7][sl] = a1.x; ring.cfg[8][sl] = a1.y; ring.cfg[9][sl] = a1.z; ring.cfg[10][sl] = a1.w;
+        ring.idx[sl] = (uint32_t)i;
+        ring.amb0[sl] = cl.amb[0];
+      }
+    }
+    __syncthreads();
+    const bool run_b = (s_tail - head) >= TGC_BLOCK;  // uniform: s_tail is stable between the two barriers
+    uint32_t e_idx = 0, e_amb = 0;
+    if (run_b) {
+      const unsigned sl = (head + threadIdx.x) & (TGC_RING - 1);
 #pragma unroll
-    for (int k = 0; k < 4; ++k) dst[k] = src[k];
-    if (valid[it.target] == 0) continue;  // edge already refuted by another sample
-    if (tg_resolve_item(g, it.cfg, it.mask, nullptr)) valid[it.target] = 0;
+      for (int k = 0; k < 11; ++k) cfg[k] = ring.cfg[k][sl];
+      e_idx = ring.idx[sl];
+      e_amb = ring.amb0[sl];
+    }
+    __syncthreads();
+    if (run_b) {
+      tg_stage_b_entry(g, thr, ex, cfg, e_idx, e_amb, valid, qu, ctr, true);
+      head += TGC_BLOCK;
+    }
+  }
+  __syncthreads();
+  const unsigned left = s_tail - head;  // < TGC_BLOCK
+  if (left) {  // uniform
+    const bool live = threadIdx.x < left;
+    float cfg[11];
+    const unsigned sl = (head + threadIdx.x) & (TGC_RING - 1);
+#pragma unroll
+    for (int k = 0; k < 11; ++k) cfg[k] = live ? ring.cfg[k][sl] : 0.f;
+    tg_stage_b_entry(g, thr, ex, cfg, live ? ring.idx[sl] : 0u, live ? ring.amb0[sl] : 0u, valid, qu, ctr, live);
   }
 }
 
-// One warp per edge.  Round j tests samples k = lane * rounds + j + 1 (k <= rake n): every round is
-// a uniform sweep over the whole segment, so a colliding edge is usually refuted in the first round
-// and the warp leaves through __any_sync.
+// ------------------------------------------------------------------------------------------------
+// phase 2: exact narrow phase over the ambiguous queue.
+// A block takes TGR_BLOCK items.  Step 1, one lane per item: FK of the 9 kernel frames and the
+// world centres of the item's ambiguous spheres, written to a shared-memory sphere list (slots
+// from a block prefix sum of the mask popcounts — no atomics, deterministic order).  Step 2, one
+// warp per sphere: tg_warp_sphere_hits.  A hit marks the item done, so its remaining spheres are
+// skipped.  Items whose sphere count exceeds the list are handled in further passes.
+// ------------------------------------------------------------------------------------------------
+#define TGR_BLOCK 128
+#define TGR_CAP 1536
+
+__device__ __forceinline__ void tg_emit_frame(const TgFrame& F, const TgBase& b, float r_pt, uint32_t bits, int k_base,
+                                              int& ord, int w0, float4* __restrict__ s_sph, uint16_t* __restrict__ s_own) {
+  while (bits) {
+    const int bit = __ffs(bits) - 1;
+    bits &= bits - 1;
+    const int slot = ord - w0;
+    ++ord;
+    if (slot < 0 || slot >= TGR_CAP) continue;
+    const float4 l = TGM_K_SPH[k_base + bit];
+    const float3 pb = tg_frame_apply(F, l.x, l.y, l.z);
+    const float3 pw = tg_to_world(b, pb.x, pb.y, pb.z);
+    s_sph[slot] = make_float4(pw.x, pw.y, pw.z, l.w + r_pt);
+    s_own[slot] = (uint16_t)threadIdx.x;
+  }
+}
+
+// bits [k0, k1) of a 128-bit mask, shifted down to bit 0 (k1 - k0 <= 32, range may straddle two words)
+__device__ __forceinline__ uint32_t tg_mask_range(const uint32_t* mask, int k0, int k1) {
+  const int w = k0 >> 5, sh = k0 & 31, n = k1 - k0;
+  uint64_t v = mask[w];
+  if (w + 1 < 4) v |= (uint64_t)mask[w + 1] << 32;
+  const uint32_t r = (uint32_t)(v >> sh);
+  return n >= 32 ? r : (r & ((1u << n) - 1u));
+}
+
+__global__ void __launch_bounds__(TGR_BLOCK) k_resolve(const TgGrid g, TgQueue qu, uint8_t* __restrict__ valid, TgCounters* ctr) {
+  __shared__ float4 s_sph[TGR_CAP];
+  __shared__ uint16_t s_own[TGR_CAP];
+  __shared__ uint32_t s_target[TGR_BLOCK];
+  __shared__ uint8_t s_done[TGR_BLOCK];
+  __shared__ int s_warp_tot[TGR_BLOCK / 32];
+  const unsigned n = min(*qu.count, qu.capacity);
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->items, (unsigned long long)n);
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (unsigned i0 = blockIdx.x * TGR_BLOCK; i0 < n; i0 += gridDim.x * TGR_BLOCK) {
+    const unsigned i = i0 + threadIdx.x;
+    TgItem it;
+    int cnt = 0;
+    if (i < n) {
+      const float4* src = reinterpret_cast<const float4*>(qu.items + i);
+      float4* dst = reinterpret_cast<float4*>(&it);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) dst[k] = src[k];
+      s_target[threadIdx.x] = it.target;
+      const bool dead = valid[it.target] == 0;  // edge already refuted by another sample
+      s_done[threadIdx.x] = dead ? 1 : 0;
+      if (!dead) cnt = __popc(it.mask[0]) + __popc(it.mask[1]) + __popc(it.mask[2]) + __popc(it.mask[3]);
+    } else {
+      s_done[threadIdx.x] = 1;
+    }
+    // block exclusive prefix sum of cnt
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp_tot[warp] = incl;
+    __syncthreads();
+    int off = incl - cnt, total = 0;
+#pragma unroll
+    for (int w = 0; w < TGR_BLOCK / 32; ++w) {
+      if (w < (int)warp) off += s_warp_tot[w];
+      total += s_warp_tot[w];
+    }
+    for (int w0 = 0; w0 < total; w0 += TGR_CAP) {  // usually a single pass
+      if (cnt > 0 && off < w0 + TGR_CAP && off + cnt > w0) {
+        const float* cfg = it.cfg;
+        const TgBase b = tg_base(cfg[0], cfg[1], cfg[2]);
+        int ord = off;
+        TgFrame T, F, H;
+        tg_frame_identity(T);
+        tg_emit_frame(T, b, g.r_pt, tg_mask_range(it.mask, 0, 20), 0, ord, w0, s_sph, s_own);
+        T.t[0] = TGM_OFF_TORSO_X;
+        T.t[2] = TGM_OFF_TORSO_Z + cfg[3];
+        tg_emit_frame(T, b, g.r_pt, tg_mask_range(it.mask, 20, 52), 20, ord, w0, s_sph, s_own);
+        tg_emit_frame(T, b, g.r_pt, tg_mask_range(it.mask, 52, 55), 52, ord, w0, s_sph, s_own);
+        if ((it.mask[1] >> 23) | it.mask[2] | it.mask[3]) {  // any arm sphere (k >= 55)
+          tg_frame_child(T, TGM_OFF_SHOULDER_PAN_X, TGM_OFF_SHOULDER_PAN_Y, TGM_OFF_SHOULDER_PAN_Z, 4, cfg[4], F);
+          tg_emit_frame(F, b, g.r_pt, tg_mask_range(it.mask, 55, 59), 55, ord, w0, s_sph, s_own);
+          tg_frame_child(F, TGM_OFF_SHOULDER_LIFT_X, TGM_OFF_SHOULDER_LIFT_Y, TGM_OFF_SHOULDER_LIFT_Z, 3, cfg[5], H);
+          tg_emit_frame(H, b, g.r_pt, tg_mask_range(it.mask, 59, 66), 59, ord, w0, s_sph, s_own);
+          tg_frame_child(H, TGM_OFF_UPPERARM_ROLL_X, TGM_OFF_UPPERARM_ROLL_Y, TGM_OFF_UPPERARM_ROLL_Z, 2, cfg[6], F);
+          tg_emit_frame(F, b, g.r_pt, tg_mask_range(it.mask, 66, 74), 66, ord, w0, s_sph, s_own);
+          tg_frame_child(F, TGM_OFF_ELBOW_FLEX_X, TGM_OFF_ELBOW_FLEX_Y, TGM_OFF_ELBOW_FLEX_Z, 3, cfg[7], H);
+          tg_emit_frame(H, b, g.r_pt, tg_mask_range(it.mask, 74, 80), 74, ord, w0, s_sph, s_own);
+          tg_frame_child(H, TGM_OFF_FOREARM_ROLL_X, TGM_OFF_FOREARM_ROLL_Y, TGM_OFF_FOREARM_ROLL_Z, 2, cfg[8], F);
+          tg_emit_frame(F, b, g.r_pt, tg_mask_range(it.mask, 80, 87), 80, ord, w0, s_sph, s_own);
+          tg_frame_child(F, TGM_OFF_WRIST_FLEX_X, TGM_OFF_WRIST_FLEX_Y, TGM_OFF_WRIST_FLEX_Z, 3, cfg[9], H);
+          tg_emit_frame(H, b, g.r_pt, tg_mask_range(it.mask, 87, 93), 87, ord, w0, s_sph, s_own);
+          tg_frame_child(H, TGM_OFF_WRIST_ROLL_X, TGM_OFF_WRIST_ROLL_Y, TGM_OFF_WRIST_ROLL_Z, 2, cfg[10], F);
+          tg_emit_frame(F, b, g.r_pt, tg_mask_range(it.mask, 93, 111), 93, ord, w0, s_sph, s_own);
+        }
+      }
+      __syncthreads();
+      const int nw = min(total - w0, TGR_CAP);
+      for (int j = (int)warp; j < nw; j += TGR_BLOCK / 32) {
+        const int own = s_own[j];
+        if (s_done[own]) continue;  // warp-uniform
+        const float4 c = s_sph[j];
+        if (tg_warp_sphere_hits(g, c.x, c.y, c.z, c.w)) {
+          if (lane == 0) {
+            s_done[own] = 1;
+            valid[s_target[own]] = 0;
+          }
+        }
+      }
+      __syncthreads();
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// edges: one warp per edge.  Round j tests samples k = lane * rounds + j + 1 (k <= rake n): every
+// round is a uniform sweep over the whole segment, so a colliding edge is usually refuted in the
+// first round and the warp leaves through __any_sync.  When the base does not move along the edge
+// (arm-only planning, plan_arm_rrtc) stage A is the same for every sample: it is evaluated once,
+// with the 20 base-pose spheres spread over the lanes (one probe instruction for the whole edge).
+// ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TG_BLOCK)
 k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm0,
               const float* __restrict__ base0, const float* __restrict__ arm1, const float* __restrict__ base1, int E, int rake,
@@ -123,6 +318,26 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
     const float inv_total = 1.0f / (float)total;
     if (lane == 0) valid[e] = 1;  // provisional; cleared below, by an inline resolve, or by phase 2
     __syncwarp();
+    // fixed base: classify the 20 base-pose spheres once, lane k <-> sphere k
+    const bool fixed_base = d[0] == 0.f && d[1] == 0.f && d[2] == 0.f;
+    uint32_t amb0_shared = 0;
+    if (fixed_base && !g.empty) {
+      const TgPose p = tg_pose(g, a[0], a[1], a[2]);
+      bool col = false, am = false;
+      if (lane < 20) {
+        const float4 l = TGM_K_SPH[lane];
+        const float gx = fmaf(p.cs, l.x, fmaf(-p.sn, l.y, p.gx0));
+        const float gy = fmaf(p.sn, l.x, fmaf(p.cs, l.y, p.gy0));
+        const int code = tg_probe(g, gx, gy, g.vpm * l.z);
+        col = code <= thr.coll_le[lane];
+        am = code < thr.free_ge[lane];
+      }
+      hit = __any_sync(0xffffffffu, col);
+      amb0_shared = __ballot_sync(0xffffffffu, am);
+      // the ambiguous base-pose spheres are the same for every sample: one item for the whole edge
+      const uint32_t m4[4] = {amb0_shared, 0u, 0u, 0u};
+      tg_push_item(g, qu, ctr, lane == 0 && amb0_shared != 0u && !hit, (uint32_t)e, m4, a, valid);
+    }
     for (int j = 0; j < rounds && !hit; ++j) {
       const int k = (int)lane * rounds + j + 1;
       const bool live = k <= total;
@@ -131,9 +346,12 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
 #pragma unroll
       for (int c = 0; c < 11; ++c) cfg[c] = fmaf(t, d[c], a[c]);
       TgClass cl;
-      cl.collide = false;
-      cl.amb[0] = cl.amb[1] = cl.amb[2] = cl.amb[3] = 0u;
-      if (live && !g.empty) tg_classify(g, thr, cfg + 3, cfg[0], cfg[1], cfg[2], cl);
+      tg_class_clear(cl);
+      if (live && !g.empty) {
+        const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
+        if (!fixed_base) tg_stage_a(g, thr, p, cl);
+        if (!cl.collide) tg_stage_b(g, thr, p, cfg + 3, cl);
+      }
       if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
       hit = __any_sync(0xffffffffu, live && cl.collide);
       if (!hit) {
@@ -199,6 +417,16 @@ __global__ void k_fill_u8(uint8_t* p, int n, uint8_t v) {
 // ------------------------------------------------------------------------------------------------
 // host entry points
 // ------------------------------------------------------------------------------------------------
+// resident blocks per SM of the two persistent kernels (queried once per env)
+int tg_query_occupancy(tg_env* env) {
+  int a = 0, b = 0;
+  TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_check_configs, TGC_BLOCK, 0));
+  TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_resolve, TGR_BLOCK, 0));
+  env->occ_configs = a > 0 ? a : 1;
+  env->occ_resolve = b > 0 ? b : 1;
+  return TG_OK;
+}
+
 static inline const TgExtras* tg_extras_ptr(const tg_env* env) {
   return (env->extras.n_obs > 0 || env->extras.n_att > 0) ? env->extras_dev : nullptr;
 }
@@ -231,11 +459,12 @@ int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int6
         for (int k = 0; k < 3; ++k) TG_CUDA(cudaEventCreate(&ev[k]));
         TG_CUDA(cudaEventRecord(ev[0], st));
       }
-      k_check_configs<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(env->grid, env->thr, ex, arm + 8 * off, base + 3 * off, nb,
-                                                                   valid + off, qu, env->counters_dev);
+      const int blocks1 = min(tg_div_up(nb, TGC_BLOCK), env->sm_count * env->occ_configs);
+      k_check_configs<<<blocks1, TGC_BLOCK, 0, st>>>(env->grid, env->thr, ex, arm + 8 * off, base + 3 * off, nb, valid + off, qu,
+                                                     env->counters_dev);
       if (env->timing) TG_CUDA(cudaEventRecord(ev[1], st));
       if (!env->grid.empty) {
-        k_resolve<<<env->sm_count * 8, TG_BLOCK, 0, st>>>(env->grid, qu, valid + off, env->counters_dev);
+        k_resolve<<<env->sm_count * env->occ_resolve, TGR_BLOCK, 0, st>>>(env->grid, qu, valid + off, env->counters_dev);
         env->launches += 1;
       }
       if (env->timing) {
@@ -269,7 +498,7 @@ int tg_check_edges_slot(tg_env* env, const float* arm0, const float* base0, cons
   if (E == 0) return TG_OK;
   const TgExtras* ex = tg_extras_ptr(env);
   TgQueue qu = tg_queue_slot(env, slot);
-  const int64_t chunk = 1 << 18;  // edges per launch pair: keeps the ambiguous queue well inside its capacity
+  const int64_t chunk = 1 << 16;  // edges per launch pair: keeps the ambiguous queue well inside its capacity
   for (int64_t off = 0; off < E; off += chunk) {
     const int ne = (int)((E - off) < chunk ? (E - off) : chunk);
     TG_CUDA(cudaMemsetAsync(qu.count, 0, sizeof(unsigned), st));
@@ -279,7 +508,7 @@ int tg_check_edges_slot(tg_env* env, const float* arm0, const float* base0, cons
                                                (unsigned long long*)n_checks, qu, env->counters_dev);
     env->launches += 1;
     if (!env->grid.empty) {
-      k_resolve<<<env->sm_count * 8, TG_BLOCK, 0, st>>>(env->grid, qu, valid + off, env->counters_dev);
+      k_resolve<<<env->sm_count * env->occ_resolve, TGR_BLOCK, 0, st>>>(env->grid, qu, valid + off, env->counters_dev);
       env->launches += 1;
     }
   }

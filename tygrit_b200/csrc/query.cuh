@@ -1,11 +1,16 @@
 // query.cuh — device functions of the fused FK + sphere-query path (K2 + K3).
 //
-// Phase 1 (tg_classify): one lane = one configuration.  The planner's robot model has the head
-// fixed, so 55 of the 111 spheres (base, torso, head) only need the SE(2) base pose and the torso
-// lift; the remaining 56 ride the 7-joint arm chain.  Every sphere centre is produced directly in
-// distance-grid coordinates (voxels) and costs ONE byte load from the L2-resident grid, giving a
-// three-way answer per sphere: definitely free / definitely colliding / ambiguous.
-// Phase 2 (tg_sphere_hits_cloud): exact test of an ambiguous sphere against the sorted cell rows.
+// Phase 1 (tg_stage_a / tg_stage_b): one lane = one configuration.  The planner's robot model has
+// the head fixed, so 55 of the 111 spheres (base, torso, head) only need the SE(2) base pose and
+// the torso lift; the remaining 56 ride the 7-joint arm chain.  Every sphere centre is produced
+// directly in distance-grid coordinates (voxels) and costs ONE byte load from the L2-resident grid,
+// giving a three-way answer per sphere: definitely free / definitely colliding / ambiguous.
+// The kernel is bound by the number of distinct L1/L2 sectors a warp's 32 random probes touch
+// (about one per clock per SM), so the spheres of every frame are ordered largest first and probed
+// in small groups: a lane whose configuration is already refuted issues no further loads.
+// Phase 2 (tg_warp_sphere_hits): exact test of an ambiguous sphere against the sorted cell rows,
+// one warp per sphere — lanes take the (z, y) cell rows, then scan the candidate points of all
+// rows together with coalesced 16-byte loads and leave through __any_sync on the first hit.
 #pragma once
 #include "common.cuh"
 #include "fk.cuh"
@@ -23,96 +28,144 @@ struct TgClass {
   uint32_t amb[4];
 };
 
-#define TG_CLASSIFY_ONE(k, code)                                 \
-  do {                                                           \
-    const int _c = (code);                                       \
-    if (_c <= thr.coll_le[k]) out.collide = true;                \
-    else if (_c < thr.free_ge[k]) out.amb[(k) >> 5] |= 1u << ((k) & 31); \
+__device__ __forceinline__ void tg_class_clear(TgClass& c) {
+  c.collide = false;
+  c.amb[0] = c.amb[1] = c.amb[2] = c.amb[3] = 0u;
+}
+
+#define TG_CLASSIFY_ONE(k, code)                                          \
+  do {                                                                    \
+    const int _c = (code);                                                \
+    out.collide |= _c <= thr.coll_le[k];                                  \
+    if (_c < thr.free_ge[k]) out.amb[(k) >> 5] |= 1u << ((k) & 31);       \
   } while (0)
 
-// spheres [K0, K1) of a frame whose rotation is the base yaw only:  p_base = l + (tx, 0, tz)
-template <int K0, int K1>
-__device__ __forceinline__ void tg_probe_yaw_frame(const TgGrid& g, const TgThr& thr, float cs, float sn, float gtx, float gty,
-                                                   float gtz, TgClass& out) {
-#pragma unroll 5
-  for (int k = K0; k < K1; ++k) {
-    const float4 l = TGM_K_SPH[k];
-    const float gx = fmaf(cs, l.x, fmaf(-sn, l.y, gtx));
-    const float gy = fmaf(sn, l.x, fmaf(cs, l.y, gty));
-    const float gz = fmaf(g.vpm, l.z, gtz);
-    TG_CLASSIFY_ONE(k, tg_probe(g, gx, gy, gz));
-  }
-}
-
-// spheres [K0, K1) of an arm frame F (base_link frame) under base pose (cs, sn, gtx0, gty0) in voxel units
-template <int K0, int K1>
-__device__ __forceinline__ void tg_probe_arm_frame(const TgGrid& g, const TgThr& thr, const TgFrame& F, float cs, float sn,
-                                                   float gtx0, float gty0, TgClass& out) {
-  // G = vpm * Rz(theta) * R ;  gt = vpm * (Rz(theta) t + p)
-  float G[9], gt[3];
-#pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    G[c] = fmaf(cs, F.r[c], -sn * F.r[3 + c]);
-    G[3 + c] = fmaf(sn, F.r[c], cs * F.r[3 + c]);
-    G[6 + c] = g.vpm * F.r[6 + c];
-  }
-  gt[0] = fmaf(cs, F.t[0], fmaf(-sn, F.t[1], gtx0));
-  gt[1] = fmaf(sn, F.t[0], fmaf(cs, F.t[1], gty0));
-  gt[2] = g.vpm * F.t[2];
-#pragma unroll 4
-  for (int k = K0; k < K1; ++k) {
-    const float4 l = TGM_K_SPH[k];
-    const float gx = fmaf(G[0], l.x, fmaf(G[1], l.y, fmaf(G[2], l.z, gt[0])));
-    const float gy = fmaf(G[3], l.x, fmaf(G[4], l.y, fmaf(G[5], l.z, gt[1])));
-    const float gz = fmaf(G[6], l.x, fmaf(G[7], l.y, fmaf(G[8], l.z, gt[2])));
-    TG_CLASSIFY_ONE(k, tg_probe(g, gx, gy, gz));
-  }
-}
-
-// Three-way classification of one configuration against the distance-bound grid.
-// q: 8 arm joints (torso first); base pose (bx, by, bth).
-__device__ __forceinline__ void tg_classify(const TgGrid& g, const TgThr& thr, const float* q, float bx, float by, float bth,
-                                            TgClass& out) {
-  out.collide = false;
-  out.amb[0] = out.amb[1] = out.amb[2] = out.amb[3] = 0u;
+// base pose in voxel units: G = vpm * Rz(theta), gt = vpm * (x, y)
+struct TgPose {
+  float cs, sn, gx0, gy0;
+};
+__device__ __forceinline__ TgPose tg_pose(const TgGrid& g, float bx, float by, float bth) {
   float s, c;
   sincosf(bth, &s, &c);
-  const float cs = g.vpm * c, sn = g.vpm * s;
-  const float gtx0 = g.vpm * bx, gty0 = g.vpm * by;
-  // frame 0: base_link + torso_fixed
-  tg_probe_yaw_frame<0, 20>(g, thr, cs, sn, gtx0, gty0, 0.f, out);
-  // frame 1: torso_lift + head (head joints fixed at 0)
+  TgPose p;
+  p.cs = g.vpm * c;
+  p.sn = g.vpm * s;
+  p.gx0 = g.vpm * bx;
+  p.gy0 = g.vpm * by;
+  return p;
+}
+
+// spheres [K0, K1) of a frame whose rotation is the base yaw only:  p_base = l + (tx, 0, tz).
+// All loads of the group are issued before the first classification (memory-level parallelism).
+template <int K0, int K1>
+__device__ __forceinline__ void tg_group_yaw(const TgGrid& g, const TgThr& thr, const TgPose& p, float gtx, float gty, float gtz,
+                                             TgClass& out) {
+  int code[K1 - K0];
+#pragma unroll
+  for (int k = K0; k < K1; ++k) {
+    const float4 l = TGM_K_SPH[k];
+    const float gx = fmaf(p.cs, l.x, fmaf(-p.sn, l.y, gtx));
+    const float gy = fmaf(p.sn, l.x, fmaf(p.cs, l.y, gty));
+    const float gz = fmaf(g.vpm, l.z, gtz);
+    code[k - K0] = tg_probe(g, gx, gy, gz);
+  }
+#pragma unroll
+  for (int k = K0; k < K1; ++k) TG_CLASSIFY_ONE(k, code[k - K0]);
+}
+
+// voxel-space affine map of an arm frame F (base_link frame) under base pose p
+struct TgVox {
+  float G[9], gt[3];
+};
+__device__ __forceinline__ void tg_vox_frame(const TgGrid& g, const TgPose& p, const TgFrame& F, TgVox& V) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    V.G[c] = fmaf(p.cs, F.r[c], -p.sn * F.r[3 + c]);
+    V.G[3 + c] = fmaf(p.sn, F.r[c], p.cs * F.r[3 + c]);
+    V.G[6 + c] = g.vpm * F.r[6 + c];
+  }
+  V.gt[0] = fmaf(p.cs, F.t[0], fmaf(-p.sn, F.t[1], p.gx0));
+  V.gt[1] = fmaf(p.sn, F.t[0], fmaf(p.cs, F.t[1], p.gy0));
+  V.gt[2] = g.vpm * F.t[2];
+}
+
+template <int K0, int K1>
+__device__ __forceinline__ void tg_group_arm(const TgGrid& g, const TgThr& thr, const TgVox& V, TgClass& out) {
+  int code[K1 - K0];
+#pragma unroll
+  for (int k = K0; k < K1; ++k) {
+    const float4 l = TGM_K_SPH[k];
+    const float gx = fmaf(V.G[0], l.x, fmaf(V.G[1], l.y, fmaf(V.G[2], l.z, V.gt[0])));
+    const float gy = fmaf(V.G[3], l.x, fmaf(V.G[4], l.y, fmaf(V.G[5], l.z, V.gt[1])));
+    const float gz = fmaf(V.G[6], l.x, fmaf(V.G[7], l.y, fmaf(V.G[8], l.z, V.gt[2])));
+    code[k - K0] = tg_probe(g, gx, gy, gz);
+  }
+#pragma unroll
+  for (int k = K0; k < K1; ++k) TG_CLASSIFY_ONE(k, code[k - K0]);
+}
+
+// Stage A: the 20 spheres that only depend on the base pose (base_link + torso_fixed), largest first.
+// Most colliding configurations are refuted by the first group of three.
+__device__ __forceinline__ void tg_stage_a(const TgGrid& g, const TgThr& thr, const TgPose& p, TgClass& out) {
+  tg_group_yaw<0, 3>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  if (out.collide) return;
+  tg_group_yaw<3, 9>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  if (out.collide) return;
+  tg_group_yaw<9, 20>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+}
+
+// Stage B: torso + head (35 spheres, base yaw + torso lift) and the 7-joint arm chain (56 spheres).
+__device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, const TgPose& p, const float* q, TgClass& out) {
   const float tz = TGM_OFF_TORSO_Z + q[0];
   {
-    const float gtx1 = fmaf(cs, TGM_OFF_TORSO_X, gtx0), gty1 = fmaf(sn, TGM_OFF_TORSO_X, gty0);
-    tg_probe_yaw_frame<20, 55>(g, thr, cs, sn, gtx1, gty1, g.vpm * tz, out);
+    const float gtx1 = fmaf(p.cs, TGM_OFF_TORSO_X, p.gx0), gty1 = fmaf(p.sn, TGM_OFF_TORSO_X, p.gy0), gtz1 = g.vpm * tz;
+    tg_group_yaw<20, 27>(g, thr, p, gtx1, gty1, gtz1, out);
+    if (out.collide) return;
+    tg_group_yaw<27, 33>(g, thr, p, gtx1, gty1, gtz1, out);
+    if (out.collide) return;
+    tg_group_yaw<33, 44>(g, thr, p, gtx1, gty1, gtz1, out);
+    if (out.collide) return;
+    tg_group_yaw<44, 55>(g, thr, p, gtx1, gty1, gtz1, out);
+    if (out.collide) return;
   }
-  if (out.collide) return;
-  // arm chain in base_link
   TgFrame T, F, H;
+  TgVox V;
   tg_frame_identity(T);
   T.t[0] = TGM_OFF_TORSO_X;
   T.t[2] = tz;
   tg_frame_child(T, TGM_OFF_SHOULDER_PAN_X, TGM_OFF_SHOULDER_PAN_Y, TGM_OFF_SHOULDER_PAN_Z, 4, q[1], F);
-  tg_probe_arm_frame<55, 59>(g, thr, F, cs, sn, gtx0, gty0, out);
+  tg_vox_frame(g, p, F, V);
+  tg_group_arm<55, 59>(g, thr, V, out);
+  if (out.collide) return;
   tg_frame_child(F, TGM_OFF_SHOULDER_LIFT_X, TGM_OFF_SHOULDER_LIFT_Y, TGM_OFF_SHOULDER_LIFT_Z, 3, q[2], H);
-  tg_probe_arm_frame<59, 66>(g, thr, H, cs, sn, gtx0, gty0, out);
+  tg_vox_frame(g, p, H, V);
+  tg_group_arm<59, 66>(g, thr, V, out);
+  if (out.collide) return;
   tg_frame_child(H, TGM_OFF_UPPERARM_ROLL_X, TGM_OFF_UPPERARM_ROLL_Y, TGM_OFF_UPPERARM_ROLL_Z, 2, q[3], F);
-  tg_probe_arm_frame<66, 74>(g, thr, F, cs, sn, gtx0, gty0, out);
+  tg_vox_frame(g, p, F, V);
+  tg_group_arm<66, 74>(g, thr, V, out);
   if (out.collide) return;
   tg_frame_child(F, TGM_OFF_ELBOW_FLEX_X, TGM_OFF_ELBOW_FLEX_Y, TGM_OFF_ELBOW_FLEX_Z, 3, q[4], H);
-  tg_probe_arm_frame<74, 80>(g, thr, H, cs, sn, gtx0, gty0, out);
+  tg_vox_frame(g, p, H, V);
+  tg_group_arm<74, 80>(g, thr, V, out);
+  if (out.collide) return;
   tg_frame_child(H, TGM_OFF_FOREARM_ROLL_X, TGM_OFF_FOREARM_ROLL_Y, TGM_OFF_FOREARM_ROLL_Z, 2, q[5], F);
-  tg_probe_arm_frame<80, 87>(g, thr, F, cs, sn, gtx0, gty0, out);
+  tg_vox_frame(g, p, F, V);
+  tg_group_arm<80, 87>(g, thr, V, out);
   if (out.collide) return;
   tg_frame_child(F, TGM_OFF_WRIST_FLEX_X, TGM_OFF_WRIST_FLEX_Y, TGM_OFF_WRIST_FLEX_Z, 3, q[6], H);
-  tg_probe_arm_frame<87, 93>(g, thr, H, cs, sn, gtx0, gty0, out);
+  tg_vox_frame(g, p, H, V);
+  tg_group_arm<87, 93>(g, thr, V, out);
+  if (out.collide) return;
   tg_frame_child(H, TGM_OFF_WRIST_ROLL_X, TGM_OFF_WRIST_ROLL_Y, TGM_OFF_WRIST_ROLL_Z, 2, q[7], F);
-  tg_probe_arm_frame<93, 111>(g, thr, F, cs, sn, gtx0, gty0, out);
+  tg_vox_frame(g, p, F, V);
+  tg_group_arm<93, 99>(g, thr, V, out);
+  if (out.collide) return;
+  tg_group_arm<99, 111>(g, thr, V, out);
 }
 
 // ------------------------------------------------------------------------------------------------
-// exact narrow phase
+// exact narrow phase, one lane per sphere (attachments, clearance output): walks the cell rows serially
 // ------------------------------------------------------------------------------------------------
 // true iff some cloud point p has |p - c|^2 <= R^2 (R already includes the point radius).
 __device__ inline bool tg_sphere_hits_cloud(const TgGrid& g, float cx, float cy, float cz, float R) {
@@ -180,6 +233,78 @@ __device__ inline float tg_sphere_clearance(const TgGrid& g, float cx, float cy,
   return sqrtf(best2) - R;
 }
 
+// ------------------------------------------------------------------------------------------------
+// exact narrow phase, one WARP per sphere (phase 2).  All 32 lanes must call it with the same
+// arguments.  Lane r of a batch owns cell row (iz, iy) of the sphere's bounding box: it clips the
+// row against the sphere (a chord in x) and reads the two cell_start entries that bracket the
+// chord — the row's candidate points are one contiguous range because x is the fastest key.  The
+// ranges of the 32 rows are then concatenated (warp prefix sum) and scanned together, 32 points per
+// step with coalesced float4 loads; the first hit ends the walk through __any_sync.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool tg_warp_sphere_hits(const TgGrid& g, float cx, float cy, float cz, float R) {
+  const unsigned lane = threadIdx.x & 31;
+  const float R2 = R * R;
+  const float Re = R + 1e-4f;
+  const float inv = 1.0f / g.cpm;
+  const int z0 = max((int)floorf((cz - Re) * g.cpm) - g.cm[2], 0), z1 = min((int)floorf((cz + Re) * g.cpm) - g.cm[2], g.cnz - 1);
+  const int y0 = max((int)floorf((cy - Re) * g.cpm) - g.cm[1], 0), y1 = min((int)floorf((cy + Re) * g.cpm) - g.cm[1], g.cny - 1);
+  const int ny = y1 - y0 + 1, nz = z1 - z0 + 1;
+  if (ny <= 0 || nz <= 0) return false;
+  const int nrows = ny * nz;
+  const float inv_ny = 1.0f / (float)ny;
+  for (int r0 = 0; r0 < nrows; r0 += 32) {
+    const int r = r0 + (int)lane;
+    uint32_t s = 0, e = 0;
+    if (r < nrows) {
+      const int jz = (int)(((float)r + 0.5f) * inv_ny);  // r / ny (exact: r < 2^20)
+      const int iz = z0 + jz, iy = y0 + (r - jz * ny);
+      const float zlo = (float)(iz + g.cm[2]) * inv, ylo = (float)(iy + g.cm[1]) * inv;
+      const float dz = fmaxf(0.f, fmaxf(zlo - cz, cz - (zlo + inv)));
+      const float dy = fmaxf(0.f, fmaxf(ylo - cy, cy - (ylo + inv)));
+      const float rx2 = Re * Re - dz * dz - dy * dy;
+      if (rx2 >= 0.f) {
+        const float rx = sqrtf(rx2) + 1e-4f;
+        const int x0 = max((int)floorf((cx - rx) * g.cpm) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpm) - g.cm[0], g.cnx - 1);
+        if (x0 <= x1) {
+          const int row = (iz * g.cny + iy) * g.cnx;
+          s = __ldg(g.cell_start + row + x0);
+          e = __ldg(g.cell_start + row + x1 + 1);
+        }
+      }
+    }
+    // concatenate the 32 ranges: inclusive prefix sum of their lengths
+    const uint32_t len = e - s;
+    uint32_t incl = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    for (uint32_t j0 = 0; j0 < total; j0 += 32) {
+      const uint32_t j = j0 + lane;
+      // owner = first lane whose inclusive sum exceeds j (binary search over the warp's registers)
+      int lo = 0;
+#pragma unroll
+      for (int step = 16; step; step >>= 1) {
+        const uint32_t v = __shfl_sync(0xffffffffu, incl, lo + step - 1);
+        if (v <= j) lo += step;
+      }
+      lo = min(lo, 31);
+      const uint32_t o_incl = __shfl_sync(0xffffffffu, incl, lo);
+      const uint32_t o_e = __shfl_sync(0xffffffffu, e, lo);
+      bool hit = false;
+      if (j < total) {
+        const float4 P = __ldg(g.pts + (o_e - (o_incl - j)));
+        const float dx = P.x - cx, dyy = P.y - cy, dzz = P.z - cz;
+        hit = fmaf(dx, dx, fmaf(dyy, dyy, dzz * dzz)) <= R2;
+      }
+      if (__any_sync(0xffffffffu, hit)) return true;
+    }
+  }
+  return false;
+}
+
 // World centre (metres) + radius of kernel-order sphere k for the planner model (head = 0).
 __device__ __forceinline__ float4 tg_sphere_world(const TgFrame* L, const TgBase& b, int k) {
   const int j = TGM_K_REF[k];
@@ -220,8 +345,8 @@ __device__ inline bool tg_extras_hit(const TgGrid& g, const TgExtras& ex, const 
   return false;
 }
 
-// Resolve an item: exact test of every ambiguous sphere; true = collision.
-__device__ inline bool tg_resolve_item(const TgGrid& g, const float* cfg, const uint32_t* mask, unsigned long long* n_pts) {
+// Resolve an item with one lane (queue-overflow fallback): exact test of every ambiguous sphere.
+__device__ inline bool tg_resolve_item(const TgGrid& g, const float* cfg, const uint32_t* mask) {
   float q10[10];
 #pragma unroll
   for (int i = 0; i < 8; ++i) q10[i] = cfg[3 + i];
@@ -229,7 +354,6 @@ __device__ inline bool tg_resolve_item(const TgGrid& g, const float* cfg, const 
   TgFrame L[TGM_N_LINKS];
   tg_fk_links(q10, L);
   const TgBase b = tg_base(cfg[0], cfg[1], cfg[2]);
-  (void)n_pts;
   for (int w = 0; w < 4; ++w) {
     uint32_t m = mask[w];
     while (m) {

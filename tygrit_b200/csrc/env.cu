@@ -456,6 +456,12 @@ extern "C" int tg_env_set_bounds(tg_env* env, const float* lo, const float* hi) 
   return TG_OK;
 }
 
+extern "C" int tg_env_set_cells_per_metre(tg_env* env, float cpm) {
+  TG_CHECK_ARG(env != nullptr && cpm >= 2.f && cpm <= 100.f, "tg_env_set_cells_per_metre: need 2 <= cells_per_metre <= 100");
+  env->cpm_requested = cpm;
+  return TG_OK;
+}
+
 extern "C" int tg_env_set_point_radius(tg_env* env, float r) {
   TG_CHECK_ARG(env != nullptr && r >= 0.f && r < 1.f, "tg_env_set_point_radius: bad argument");
   env->r_pt = r;

@@ -162,8 +162,9 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
 // warp per sphere: tg_warp_sphere_hits.  A hit marks the item done, so its remaining spheres are
 // skipped.  Items whose sphere count exceeds the list are handled in further passes.
 // ------------------------------------------------------------------------------------------------
-#define TGR_BLOCK 128
-#define TGR_CAP 1536
+#define TGR_BLOCK 128   // threads per block
+#define TGR_ITEMS 64    // queue items per batch: small batches keep the serial sphere chain per warp short
+#define TGR_CAP 1024    // sphere-list slots per pass
 
 __device__ __forceinline__ void tg_emit_frame(const TgFrame& F, const TgBase& b, float r_pt, uint32_t bits, int k_base,
                                               int& ord, int w0, float4* __restrict__ s_sph, uint16_t* __restrict__ s_own) {
@@ -190,30 +191,38 @@ __device__ __forceinline__ uint32_t tg_mask_range(const uint32_t* mask, int k0, 
   return n >= 32 ? r : (r & ((1u << n) - 1u));
 }
 
-__global__ void __launch_bounds__(TGR_BLOCK) k_resolve(const TgGrid g, TgQueue qu, uint8_t* __restrict__ valid, TgCounters* ctr) {
+__global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueue qu, uint8_t* __restrict__ valid, TgCounters* ctr) {
   __shared__ float4 s_sph[TGR_CAP];
   __shared__ uint16_t s_own[TGR_CAP];
-  __shared__ uint32_t s_target[TGR_BLOCK];
-  __shared__ uint8_t s_done[TGR_BLOCK];
+  __shared__ uint32_t s_target[TGR_ITEMS];
+  __shared__ uint8_t s_done[TGR_ITEMS];
   __shared__ int s_warp_tot[TGR_BLOCK / 32];
+  __shared__ unsigned s_batch;
   const unsigned n = min(*qu.count, qu.capacity);
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->items, (unsigned long long)n);
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (unsigned i0 = blockIdx.x * TGR_BLOCK; i0 < n; i0 += gridDim.x * TGR_BLOCK) {
-    const unsigned i = i0 + threadIdx.x;
+  const unsigned nbatch = (n + TGR_ITEMS - 1) / TGR_ITEMS;
+  for (;;) {
+    if (threadIdx.x == 0) s_batch = atomicAdd(qu.count + 1, 1u);  // batches are handed out dynamically
+    __syncthreads();
+    const unsigned batch = s_batch;
+    if (batch >= nbatch) break;
+    const unsigned i = batch * TGR_ITEMS + threadIdx.x;
     TgItem it;
     int cnt = 0;
-    if (i < n) {
-      const float4* src = reinterpret_cast<const float4*>(qu.items + i);
-      float4* dst = reinterpret_cast<float4*>(&it);
+    if (threadIdx.x < TGR_ITEMS) {
+      if (i < n) {
+        const float4* src = reinterpret_cast<const float4*>(qu.items + i);
+        float4* dst = reinterpret_cast<float4*>(&it);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) dst[k] = src[k];
-      s_target[threadIdx.x] = it.target;
-      const bool dead = valid[it.target] == 0;  // edge already refuted by another sample
-      s_done[threadIdx.x] = dead ? 1 : 0;
-      if (!dead) cnt = __popc(it.mask[0]) + __popc(it.mask[1]) + __popc(it.mask[2]) + __popc(it.mask[3]);
-    } else {
-      s_done[threadIdx.x] = 1;
+        for (int k = 0; k < 4; ++k) dst[k] = src[k];
+        s_target[threadIdx.x] = it.target;
+        const bool dead = valid[it.target] == 0;  // edge already refuted by another sample
+        s_done[threadIdx.x] = dead ? 1 : 0;
+        if (!dead) cnt = __popc(it.mask[0]) + __popc(it.mask[1]) + __popc(it.mask[2]) + __popc(it.mask[3]);
+      } else {
+        s_done[threadIdx.x] = 1;
+      }
     }
     // block exclusive prefix sum of cnt
     int incl = cnt;
@@ -453,7 +462,7 @@ int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int6
       k_fill_u8<<<tg_div_up(nb, 256), 256, 0, st>>>(valid + off, nb, 1);
       env->launches += 1;
     } else {
-      TG_CUDA(cudaMemsetAsync(qu.count, 0, sizeof(unsigned), st));
+      TG_CUDA(cudaMemsetAsync(qu.count, 0, 2 * sizeof(unsigned), st));
       cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
       if (env->timing) {
         for (int k = 0; k < 3; ++k) TG_CUDA(cudaEventCreate(&ev[k]));
@@ -501,7 +510,7 @@ int tg_check_edges_slot(tg_env* env, const float* arm0, const float* base0, cons
   const int64_t chunk = 1 << 16;  // edges per launch pair: keeps the ambiguous queue well inside its capacity
   for (int64_t off = 0; off < E; off += chunk) {
     const int ne = (int)((E - off) < chunk ? (E - off) : chunk);
-    TG_CUDA(cudaMemsetAsync(qu.count, 0, sizeof(unsigned), st));
+    TG_CUDA(cudaMemsetAsync(qu.count, 0, 2 * sizeof(unsigned), st));
     const int blocks = min(tg_div_up(ne, TG_BLOCK / 32), env->sm_count * 16);
     k_check_edges<<<blocks, TG_BLOCK, 0, st>>>(env->grid, env->thr, ex, arm0 + 8 * off, base0 + 3 * off, arm1 + 8 * off,
                                                base1 + 3 * off, ne, rake, resolution, valid + off,

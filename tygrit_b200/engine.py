@@ -74,6 +74,10 @@ class CollisionWorld:
     def set_point_radius(self, r: float) -> None:
         N.check(self._lib.tg_env_set_point_radius(self._h, float(r)), "tg_env_set_point_radius")
 
+    def set_cells_per_metre(self, cpm: float) -> None:
+        """Resolution of the narrow-phase cell grid, used by the next :meth:`build`."""
+        N.check(self._lib.tg_env_set_cells_per_metre(self._h, float(cpm)), "tg_env_set_cells_per_metre")
+
     def set_bounds(self, lo=None, hi=None) -> None:
         if lo is None or hi is None:
             N.check(self._lib.tg_env_set_bounds(self._h, None, None), "tg_env_set_bounds")

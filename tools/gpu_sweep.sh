@@ -1,7 +1,8 @@
 #!/bin/bash
 # parameter sweep of the config-check bench (short runs, no e2e / cpu legs)
 mkdir -p gpurun_out
-for args in "--vpm 50 --cpm 25" "--vpm 50 --cpm 16" "--vpm 50 --cpm 12.5" "--vpm 50 --cpm 10" "--vpm 50 --cpm 8" "--vpm 66 --cpm 12.5" "--vpm 40 --cpm 12.5"; do
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+for args in "--vpm 50" "--vpm 58" "--vpm 66" "--vpm 66 --cpm 25" "--vpm 80 --cpm 25" "--vpm 100 --cpm 25"; do
   python bench.py --configs 16777216 --steps 3 --warmup 3 --no-e2e --no-cpu $args > gpurun_out/sweep.json 2> gpurun_out/sweep.err || tail -3 gpurun_out/sweep.err
   python - "$args" <<'PY'
 import json,sys

@@ -241,66 +241,85 @@ __device__ inline float tg_sphere_clearance(const TgGrid& g, float cx, float cy,
 // ranges of the 32 rows are then concatenated (warp prefix sum) and scanned together, 32 points per
 // step with coalesced float4 loads; the first hit ends the walk through __any_sync.
 // ------------------------------------------------------------------------------------------------
+struct TgRows {  // cell rows of a sphere's bounding box
+  int z0, y0, ny, nrows;
+  float inv_ny;
+};
+__device__ __forceinline__ TgRows tg_rows(const TgGrid& g, float cy, float cz, float Re) {
+  TgRows w;
+  w.z0 = max((int)floorf((cz - Re) * g.cpm) - g.cm[2], 0);
+  w.y0 = max((int)floorf((cy - Re) * g.cpm) - g.cm[1], 0);
+  const int z1 = min((int)floorf((cz + Re) * g.cpm) - g.cm[2], g.cnz - 1);
+  const int y1 = min((int)floorf((cy + Re) * g.cpm) - g.cm[1], g.cny - 1);
+  w.ny = y1 - w.y0 + 1;
+  const int nz = z1 - w.z0 + 1;
+  w.nrows = (w.ny > 0 && nz > 0) ? w.ny * nz : 0;
+  w.inv_ny = 1.0f / (float)max(w.ny, 1);
+  return w;
+}
+
+// candidate point range [s, e) of row r (this lane's row): the chord of the sphere in that row
+__device__ __forceinline__ void tg_row_range(const TgGrid& g, const TgRows& w, float cx, float cy, float cz, float Re, int r,
+                                             uint32_t& s, uint32_t& e) {
+  s = e = 0;
+  if (r >= w.nrows) return;
+  const float inv = 1.0f / g.cpm;
+  const int jz = (int)(((float)r + 0.5f) * w.inv_ny);  // r / ny (exact: r < 2^20)
+  const int iz = w.z0 + jz, iy = w.y0 + (r - jz * w.ny);
+  const float zlo = (float)(iz + g.cm[2]) * inv, ylo = (float)(iy + g.cm[1]) * inv;
+  const float dz = fmaxf(0.f, fmaxf(zlo - cz, cz - (zlo + inv)));
+  const float dy = fmaxf(0.f, fmaxf(ylo - cy, cy - (ylo + inv)));
+  const float rx2 = Re * Re - dz * dz - dy * dy;
+  if (rx2 < 0.f) return;
+  const float rx = sqrtf(rx2) + 1e-4f;
+  const int x0 = max((int)floorf((cx - rx) * g.cpm) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpm) - g.cm[0], g.cnx - 1);
+  if (x0 > x1) return;
+  const int row = (iz * g.cny + iy) * g.cnx;
+  s = __ldg(g.cell_start + row + x0);
+  e = __ldg(g.cell_start + row + x1 + 1);
+}
+
+// scan the concatenation of the 32 lanes' ranges, 32 points per step; warp-uniform result
+__device__ __forceinline__ bool tg_scan_ranges(const TgGrid& g, float cx, float cy, float cz, float R2, uint32_t s, uint32_t e) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t len = e - s;
+  uint32_t incl = len;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((int)lane >= o) incl += t;
+  }
+  const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+  for (uint32_t j0 = 0; j0 < total; j0 += 32) {
+    const uint32_t j = j0 + lane;
+    int lo = 0;  // owner = first lane whose inclusive sum exceeds j (binary search over the warp's registers)
+#pragma unroll
+    for (int step = 16; step; step >>= 1) {
+      const uint32_t v = __shfl_sync(0xffffffffu, incl, lo + step - 1);
+      if (v <= j) lo += step;
+    }
+    lo = min(lo, 31);
+    const uint32_t o_incl = __shfl_sync(0xffffffffu, incl, lo);
+    const uint32_t o_e = __shfl_sync(0xffffffffu, e, lo);
+    bool hit = false;
+    if (j < total) {
+      const float4 P = __ldg(g.pts + (o_e - (o_incl - j)));
+      const float dx = P.x - cx, dyy = P.y - cy, dzz = P.z - cz;
+      hit = fmaf(dx, dx, fmaf(dyy, dyy, dzz * dzz)) <= R2;
+    }
+    if (__any_sync(0xffffffffu, hit)) return true;
+  }
+  return false;
+}
+
 __device__ __forceinline__ bool tg_warp_sphere_hits(const TgGrid& g, float cx, float cy, float cz, float R) {
   const unsigned lane = threadIdx.x & 31;
-  const float R2 = R * R;
   const float Re = R + 1e-4f;
-  const float inv = 1.0f / g.cpm;
-  const int z0 = max((int)floorf((cz - Re) * g.cpm) - g.cm[2], 0), z1 = min((int)floorf((cz + Re) * g.cpm) - g.cm[2], g.cnz - 1);
-  const int y0 = max((int)floorf((cy - Re) * g.cpm) - g.cm[1], 0), y1 = min((int)floorf((cy + Re) * g.cpm) - g.cm[1], g.cny - 1);
-  const int ny = y1 - y0 + 1, nz = z1 - z0 + 1;
-  if (ny <= 0 || nz <= 0) return false;
-  const int nrows = ny * nz;
-  const float inv_ny = 1.0f / (float)ny;
-  for (int r0 = 0; r0 < nrows; r0 += 32) {
-    const int r = r0 + (int)lane;
-    uint32_t s = 0, e = 0;
-    if (r < nrows) {
-      const int jz = (int)(((float)r + 0.5f) * inv_ny);  // r / ny (exact: r < 2^20)
-      const int iz = z0 + jz, iy = y0 + (r - jz * ny);
-      const float zlo = (float)(iz + g.cm[2]) * inv, ylo = (float)(iy + g.cm[1]) * inv;
-      const float dz = fmaxf(0.f, fmaxf(zlo - cz, cz - (zlo + inv)));
-      const float dy = fmaxf(0.f, fmaxf(ylo - cy, cy - (ylo + inv)));
-      const float rx2 = Re * Re - dz * dz - dy * dy;
-      if (rx2 >= 0.f) {
-        const float rx = sqrtf(rx2) + 1e-4f;
-        const int x0 = max((int)floorf((cx - rx) * g.cpm) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpm) - g.cm[0], g.cnx - 1);
-        if (x0 <= x1) {
-          const int row = (iz * g.cny + iy) * g.cnx;
-          s = __ldg(g.cell_start + row + x0);
-          e = __ldg(g.cell_start + row + x1 + 1);
-        }
-      }
-    }
-    // concatenate the 32 ranges: inclusive prefix sum of their lengths
-    const uint32_t len = e - s;
-    uint32_t incl = len;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-      if ((int)lane >= o) incl += t;
-    }
-    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-    for (uint32_t j0 = 0; j0 < total; j0 += 32) {
-      const uint32_t j = j0 + lane;
-      // owner = first lane whose inclusive sum exceeds j (binary search over the warp's registers)
-      int lo = 0;
-#pragma unroll
-      for (int step = 16; step; step >>= 1) {
-        const uint32_t v = __shfl_sync(0xffffffffu, incl, lo + step - 1);
-        if (v <= j) lo += step;
-      }
-      lo = min(lo, 31);
-      const uint32_t o_incl = __shfl_sync(0xffffffffu, incl, lo);
-      const uint32_t o_e = __shfl_sync(0xffffffffu, e, lo);
-      bool hit = false;
-      if (j < total) {
-        const float4 P = __ldg(g.pts + (o_e - (o_incl - j)));
-        const float dx = P.x - cx, dyy = P.y - cy, dzz = P.z - cz;
-        hit = fmaf(dx, dx, fmaf(dyy, dyy, dzz * dzz)) <= R2;
-      }
-      if (__any_sync(0xffffffffu, hit)) return true;
-    }
+  const TgRows w = tg_rows(g, cy, cz, Re);
+  for (int r0 = 0; r0 < w.nrows; r0 += 32) {
+    uint32_t s, e;
+    tg_row_range(g, w, cx, cy, cz, Re, r0 + (int)lane, s, e);
+    if (tg_scan_ranges(g, cx, cy, cz, R * R, s, e)) return true;
   }
   return false;
 }

@@ -288,6 +288,11 @@ static void tg_compute_thresholds(const TgGrid& g, TgThr* thr) {
     thr->free_ge[j] = fg;
     thr->coll_le[j] = cl;
   }
+  for (int b = 0; b < 16; ++b) thr->bound_ge[b] = 256;  // never
+  for (int b = 0; b < TGM_N_BOUNDS; ++b) {
+    const double R = (double)TGM_H_BOUND_RADIUS[b] + (double)g.r_pt;
+    thr->bound_ge[b] = (int)floor((R + slack) / q) + 1;  // > 255: the window is too small to ever prove it
+  }
 }
 
 // choose grid geometry for the cloud box [lo, hi]; returns false if it cannot fit

@@ -114,19 +114,46 @@ __device__ __forceinline__ void tg_stage_a(const TgGrid& g, const TgThr& thr, co
   tg_group_yaw<9, 20>(g, thr, p, p.gx0, p.gy0, 0.f, out);
 }
 
+// enclosing-sphere probes (cull groups, fetch_model.cuh TGM_BOUND): true = the whole group is free
+template <int B>
+__device__ __forceinline__ int tg_bound_code_yaw(const TgGrid& g, const TgPose& p, float gtx, float gty, float gtz) {
+  const float4 l = TGM_BOUND[B];
+  return tg_probe(g, fmaf(p.cs, l.x, fmaf(-p.sn, l.y, gtx)), fmaf(p.sn, l.x, fmaf(p.cs, l.y, gty)), fmaf(g.vpm, l.z, gtz));
+}
+template <int B>
+__device__ __forceinline__ bool tg_bound_free_arm(const TgGrid& g, const TgThr& thr, const TgVox& V) {
+  const float4 l = TGM_BOUND[B];
+  const float gx = fmaf(V.G[0], l.x, fmaf(V.G[1], l.y, fmaf(V.G[2], l.z, V.gt[0])));
+  const float gy = fmaf(V.G[3], l.x, fmaf(V.G[4], l.y, fmaf(V.G[5], l.z, V.gt[1])));
+  const float gz = fmaf(V.G[6], l.x, fmaf(V.G[7], l.y, fmaf(V.G[8], l.z, V.gt[2])));
+  return tg_probe(g, gx, gy, gz) >= thr.bound_ge[B];
+}
+
 // Stage B: torso + head (35 spheres, base yaw + torso lift) and the 7-joint arm chain (56 spheres).
+// The small spheres are grouped (head, ears, one group per arm link); one probe at the centre of a
+// group's enclosing sphere that proves it free skips the whole group, which is the common case for a
+// free configuration away from the surfaces.
 __device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, const TgPose& p, const float* q, TgClass& out) {
   const float tz = TGM_OFF_TORSO_Z + q[0];
   {
     const float gtx1 = fmaf(p.cs, TGM_OFF_TORSO_X, p.gx0), gty1 = fmaf(p.sn, TGM_OFF_TORSO_X, p.gy0), gtz1 = g.vpm * tz;
-    tg_group_yaw<20, 27>(g, thr, p, gtx1, gty1, gtz1, out);
+    const int b0 = tg_bound_code_yaw<0>(g, p, gtx1, gty1, gtz1);
+    const int b1 = tg_bound_code_yaw<1>(g, p, gtx1, gty1, gtz1);
+    const int b2 = tg_bound_code_yaw<2>(g, p, gtx1, gty1, gtz1);
+    tg_group_yaw<20, 28>(g, thr, p, gtx1, gty1, gtz1, out);
     if (out.collide) return;
-    tg_group_yaw<27, 33>(g, thr, p, gtx1, gty1, gtz1, out);
-    if (out.collide) return;
-    tg_group_yaw<33, 44>(g, thr, p, gtx1, gty1, gtz1, out);
-    if (out.collide) return;
-    tg_group_yaw<44, 55>(g, thr, p, gtx1, gty1, gtz1, out);
-    if (out.collide) return;
+    if (b0 < thr.bound_ge[0]) {
+      tg_group_yaw<28, 33>(g, thr, p, gtx1, gty1, gtz1, out);
+      if (out.collide) return;
+    }
+    if (b1 < thr.bound_ge[1]) {
+      tg_group_yaw<33, 44>(g, thr, p, gtx1, gty1, gtz1, out);
+      if (out.collide) return;
+    }
+    if (b2 < thr.bound_ge[2]) {
+      tg_group_yaw<44, 55>(g, thr, p, gtx1, gty1, gtz1, out);
+      if (out.collide) return;
+    }
   }
   TgFrame T, F, H;
   TgVox V;
@@ -135,33 +162,47 @@ __device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, co
   T.t[2] = tz;
   tg_frame_child(T, TGM_OFF_SHOULDER_PAN_X, TGM_OFF_SHOULDER_PAN_Y, TGM_OFF_SHOULDER_PAN_Z, 4, q[1], F);
   tg_vox_frame(g, p, F, V);
-  tg_group_arm<55, 59>(g, thr, V, out);
-  if (out.collide) return;
+  if (!tg_bound_free_arm<3>(g, thr, V)) {
+    tg_group_arm<55, 59>(g, thr, V, out);
+    if (out.collide) return;
+  }
   tg_frame_child(F, TGM_OFF_SHOULDER_LIFT_X, TGM_OFF_SHOULDER_LIFT_Y, TGM_OFF_SHOULDER_LIFT_Z, 3, q[2], H);
   tg_vox_frame(g, p, H, V);
-  tg_group_arm<59, 66>(g, thr, V, out);
-  if (out.collide) return;
+  if (!tg_bound_free_arm<4>(g, thr, V)) {
+    tg_group_arm<59, 66>(g, thr, V, out);
+    if (out.collide) return;
+  }
   tg_frame_child(H, TGM_OFF_UPPERARM_ROLL_X, TGM_OFF_UPPERARM_ROLL_Y, TGM_OFF_UPPERARM_ROLL_Z, 2, q[3], F);
   tg_vox_frame(g, p, F, V);
-  tg_group_arm<66, 74>(g, thr, V, out);
-  if (out.collide) return;
+  if (!tg_bound_free_arm<5>(g, thr, V)) {
+    tg_group_arm<66, 74>(g, thr, V, out);
+    if (out.collide) return;
+  }
   tg_frame_child(F, TGM_OFF_ELBOW_FLEX_X, TGM_OFF_ELBOW_FLEX_Y, TGM_OFF_ELBOW_FLEX_Z, 3, q[4], H);
   tg_vox_frame(g, p, H, V);
-  tg_group_arm<74, 80>(g, thr, V, out);
-  if (out.collide) return;
+  if (!tg_bound_free_arm<6>(g, thr, V)) {
+    tg_group_arm<74, 80>(g, thr, V, out);
+    if (out.collide) return;
+  }
   tg_frame_child(H, TGM_OFF_FOREARM_ROLL_X, TGM_OFF_FOREARM_ROLL_Y, TGM_OFF_FOREARM_ROLL_Z, 2, q[5], F);
   tg_vox_frame(g, p, F, V);
-  tg_group_arm<80, 87>(g, thr, V, out);
-  if (out.collide) return;
+  if (!tg_bound_free_arm<7>(g, thr, V)) {
+    tg_group_arm<80, 87>(g, thr, V, out);
+    if (out.collide) return;
+  }
   tg_frame_child(F, TGM_OFF_WRIST_FLEX_X, TGM_OFF_WRIST_FLEX_Y, TGM_OFF_WRIST_FLEX_Z, 3, q[6], H);
   tg_vox_frame(g, p, H, V);
-  tg_group_arm<87, 93>(g, thr, V, out);
-  if (out.collide) return;
+  if (!tg_bound_free_arm<8>(g, thr, V)) {
+    tg_group_arm<87, 93>(g, thr, V, out);
+    if (out.collide) return;
+  }
   tg_frame_child(H, TGM_OFF_WRIST_ROLL_X, TGM_OFF_WRIST_ROLL_Y, TGM_OFF_WRIST_ROLL_Z, 2, q[7], F);
   tg_vox_frame(g, p, F, V);
-  tg_group_arm<93, 99>(g, thr, V, out);
-  if (out.collide) return;
-  tg_group_arm<99, 111>(g, thr, V, out);
+  if (!tg_bound_free_arm<9>(g, thr, V)) {
+    tg_group_arm<93, 99>(g, thr, V, out);
+    if (out.collide) return;
+    tg_group_arm<99, 111>(g, thr, V, out);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------

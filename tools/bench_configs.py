@@ -1,0 +1,160 @@
+#!/usr/bin/env python
+"""Secondary benchmark lines for the BASELINE.json configurations that are not bench.py's headline.
+
+  C1  4096 random configs vs 50k-point tabletop cloud          (latency of one call, device + host API)
+  C2  100k random arm edges vs 200k-point room cloud            (edges/s, config checks/s)
+  C3  self-filter, 640x480 depth x 1024 robot states            (pixels/s, GB/s vs HBM peak, 5 B/pixel)
+  C5  100 steps x (cloud rebuild + 1M edges)                    (steps/s, build us, edges/s)
+
+One JSON line per configuration on stdout.  Inputs are synthetic (tygrit_b200/synth.py) and resident
+on the device unless the line says "host".  Run on one GPU: python tools/bench_configs.py [--only C2]
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from tygrit_b200 import _native as N  # noqa: E402
+from tygrit_b200 import engine, synth  # noqa: E402
+from tygrit_b200.engine import CollisionWorld  # noqa: E402
+
+
+def cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def timed(fn, reps, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    return float(json.load(open(p))["hbm_gbs"]) if os.path.exists(p) else 6650.0
+
+
+def c1(args):
+    cloud = synth.tabletop_cloud(50_000)
+    w = CollisionWorld(max_points=1 << 20, voxels_per_metre=args.vpm)
+    w.build(cuda(cloud))
+    arm, base = synth.random_configs(4096, base_box=(-1, 1, -1, 1))
+    a, b = cuda(arm), cuda(base)
+    v = torch.empty(4096, dtype=torch.uint8, device="cuda")
+    ms = timed(lambda: w.check_configs_into(a, b, v), 200)
+    t0 = time.perf_counter()
+    for _ in range(50):
+        hv = w.check_configs_host(arm, base)
+    host_ms = (time.perf_counter() - t0) / 50 * 1e3
+    return {"config": "C1: 4096 configs vs 50k-point tabletop cloud", "device_call_us": ms * 1e3, "configs_per_s": 4096 / (ms * 1e-3),
+            "host_call_us": host_ms * 1e3, "host_configs_per_s": 4096 / (host_ms * 1e-3), "free_fraction": float(hv.mean())}
+
+
+def c2(args):
+    cloud = synth.room_cloud(200_000)
+    w = CollisionWorld(max_points=1 << 20, voxels_per_metre=args.vpm)
+    w.build(cuda(cloud))
+    out = {}
+    for name, rrt in (("uniform", False), ("rrt_like", True)):
+        e = [cuda(x) for x in synth.random_edges(100_000, rrt_like=rrt)]
+        valid, n = w.check_edges(*e, count=True)
+        checks = int(n.item())
+        ms = timed(lambda: w.check_edges(*e), 10)
+        out[name] = {"ms": ms, "edges_per_s": 1e5 / (ms * 1e-3), "config_checks": checks,
+                     "config_checks_per_s": checks / (ms * 1e-3), "valid_fraction": float(valid.float().mean().item())}
+    return {"config": "C2: 100k random Fetch edges (rake 8, resolution 32) vs 200k-point room cloud", **out}
+
+
+def c3(args):
+    S, H, W = args.states, 480, 640
+    states = cuda(synth.random_states(S))
+    boxes = synth.room_boxes()
+    bx = cuda(np.array([[*lo, *hi] for lo, hi in boxes], np.float32))
+    depth = torch.empty(S, H, W, device="cuda")
+    K = np.ascontiguousarray(synth.HEAD_CAMERA_K)
+    N.check(N.lib().tg_synth_depth(states.data_ptr(), S, bx.data_ptr(), len(boxes), H, W, K.ctypes.data, 0.0, 1,
+                                   depth.data_ptr(), None), "tg_synth_depth")
+    mask = torch.empty(S, H, W, dtype=torch.uint8, device="cuda")
+    ms = timed(lambda: engine.self_filter_depth(depth, K, states, 0.08, (0.2, 3.0), 1, mask=mask), 10)
+    px = S * H * W
+    gbs = px * 5 / (ms * 1e-3) / 1e9
+    ms4 = timed(lambda: engine.self_filter_depth(depth, K, states, 0.08, (0.2, 3.0), 4), 10)
+    valid = depth > 0
+    return {"config": f"C3: robot self-filter, {W}x{H} depth x {S} states", "ms": ms, "pixels_per_s": px / (ms * 1e-3),
+            "frames_per_s": S / (ms * 1e-3), "algorithmic_GBps": gbs, "hbm_peak_GBps": hbm_peak(), "frac_of_hbm": gbs / hbm_peak(),
+            "stride4_ms": ms4, "kept_fraction": float(mask.float().mean().item()), "valid_depth_fraction": float(valid.float().mean().item()),
+            "robot_pixels_fraction": float((valid & (mask == 0) & (depth >= 0.2) & (depth <= 3.0)).float().mean().item())}
+
+
+def c5(args):
+    steps, E = args.steps, args.edges
+    w = CollisionWorld(max_points=1 << 20, voxels_per_metre=args.vpm)
+    w.set_bounds((-4.2, -3.2, 0.2), (4.2, 3.2, 2.8))          # fixed workspace: the build never synchronises
+    clouds = [cuda(synth.room_cloud(200_000 + 100_000 * (i % 4), perturb_step=i)) for i in range(8)]
+    e = [cuda(x) for x in synth.random_edges(E)]
+    valid = torch.empty(E, dtype=torch.uint8, device="cuda")
+
+    def step(i):
+        w.build(clouds[i % len(clouds)])
+        return w.check_edges(*e)
+
+    for i in range(3):
+        step(i)
+    torch.cuda.synchronize()
+    _, n = w.check_edges(*e, count=True)
+    checks = int(n.item())
+    eb = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    build_ms = 0.0
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        eb[0].record()
+        w.build(clouds[i % len(clouds)])
+        eb[1].record()
+        valid = w.check_edges(*e)
+        if i % 10 == 0:
+            torch.cuda.synchronize()
+            build_ms += eb[0].elapsed_time(eb[1])
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    return {"config": f"C5: {steps} steps x (rebuild 200k-500k-point cloud + {E} edges)", "steps_per_s": steps / dt,
+            "ms_per_step": dt / steps * 1e3, "build_us": build_ms / ((steps + 9) // 10) * 1e3, "edges_per_s": steps * E / dt,
+            "config_checks_per_s": steps * checks / dt, "valid_fraction": float(valid.float().mean().item())}
+
+
+def main():
+    p = argparse.ArgumentParser()
+    p.add_argument("--only", default="")
+    p.add_argument("--vpm", type=float, default=50.0)
+    p.add_argument("--states", type=int, default=1024)
+    p.add_argument("--steps", type=int, default=100)
+    p.add_argument("--edges", type=int, default=1_000_000)
+    args = p.parse_args()
+    assert torch.cuda.is_available(), "needs a CUDA device"
+    for name, fn in (("C1", c1), ("C2", c2), ("C3", c3), ("C5", c5)):
+        if args.only and name not in args.only.split(","):
+            continue
+        r = fn(args)
+        r["voxels_per_metre"] = args.vpm
+        print(json.dumps(r), flush=True)
+
+
+if __name__ == "__main__":
+    main()

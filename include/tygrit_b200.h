@@ -134,6 +134,11 @@ int tg_check_edges_host(tg_env* env, const float* arm0, const float* base0, cons
  * queue overflows handled inline, kernels launched.                              */
 int tg_env_counters(tg_env* env, int64_t* out4, void* stream);
 
+/* Narrow-phase work counters of a -DTG_STATS profiling build (HOST out, 16 int64; all zero in
+ * the product build): [1] spheres listed, [2] spheres walked, [3] row batches, [4] 32-point scan
+ * steps, [5..7] walked spheres by radius class, [8] hits, [9] candidate points.              */
+int tg_debug_stats(int64_t* out16, int reset);
+
 /* Device-time instrumentation for benchmarking: when on, tg_check_configs brackets its
  * phase-1 (FK + grid classification) and phase-2 (exact narrow phase) launches with CUDA
  * events on the launching stream.  tg_env_timing_read waits for them and returns

@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libtygrit_b200.so")
+LIB_PATH = os.environ.get("TYGRIT_B200_LIB") or os.path.join(_HERE, "lib", "libtygrit_b200.so")
 
 TG_N_SPHERES = 111
 TG_N_LINKS = 15
@@ -38,6 +38,7 @@ _SIGS = {
     "tg_env_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "tg_env_timing_read": (C.c_int, [C.c_void_p, C.c_void_p]),
     "tg_env_counters": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "tg_debug_stats": (C.c_int, [C.c_void_p, C.c_int]),
     "tg_fk_spheres": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "tg_fk_frames": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "tg_check_configs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),

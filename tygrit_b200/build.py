@@ -37,8 +37,17 @@ def nvcc_path() -> str:
     raise RuntimeError("nvcc not found: the tygrit_b200 CUDA library cannot be built")
 
 
-def build_cuda(force: bool = False, verbose: bool = False) -> str:
+def build_cuda(force: bool = False, verbose: bool = False, stats: bool = False) -> str:
+    """``stats=True`` builds ``libtygrit_b200_stats.so`` with -DTG_STATS (narrow-phase work counters,
+    a profiling aid selected with TYGRIT_B200_LIB; never the product library)."""
     os.makedirs(LIBDIR, exist_ok=True)
+    if stats:
+        return _build(os.path.join(LIBDIR, "libtygrit_b200_stats.so"), os.path.join(LIBDIR, "stats"), ["-DTG_STATS"], force, verbose)
+    return _build(LIB, LIBDIR, [], force, verbose)
+
+
+def _build(LIB: str, OBJDIR: str, extra: list[str], force: bool, verbose: bool) -> str:
+    os.makedirs(OBJDIR, exist_ok=True)
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     deps.append(os.path.join(ROOT, "include", "tygrit_b200.h"))
@@ -47,9 +56,9 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
     objs = []
     procs = []
     for s in srcs:
-        o = os.path.join(LIBDIR, os.path.basename(s).replace(".cu", ".o"))
+        o = os.path.join(OBJDIR, os.path.basename(s).replace(".cu", ".o"))
         objs.append(o)
-        cmd = [nvcc_path(), *NVCC_FLAGS, "-c", s, "-o", o]
+        cmd = [nvcc_path(), *NVCC_FLAGS, *extra, "-c", s, "-o", o]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
@@ -81,4 +90,6 @@ def build_oracle(force: bool = False) -> str | None:
 
 if __name__ == "__main__":
     print(build_cuda(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--stats" in sys.argv:
+        print(build_cuda(force="--force" in sys.argv, stats=True))
     print(build_oracle(force="--force" in sys.argv))

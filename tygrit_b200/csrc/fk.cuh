@@ -9,6 +9,41 @@
 #include "common.cuh"
 #include "fetch_model.cuh"
 
+// sin/cos with a short inline fast path (|x| < 1000: three-term Cody-Waite reduction by pi/2 and
+// degree-7/8 minimax polynomials, <= 1.5 ulp, checked against fp64 in tests/test_oracle.py) and ONE
+// shared out-of-line slow path.  The library sincosf inlines its Payne-Hanek branch at every call
+// site; with eight joints per configuration that was a quarter of the query kernels' code and
+// showed up as instruction-cache stalls.
+static __device__ __noinline__ void tg_sincos_slow(float x, float* s, float* c) { sincosf(x, s, c); }
+
+__device__ __forceinline__ void tg_sincos(float x, float* sn, float* cs) {
+  if (!(fabsf(x) < 1000.0f)) {
+    tg_sincos_slow(x, sn, cs);
+    return;
+  }
+  const float k = rintf(x * 0.636619747f);
+  float r = fmaf(k, -1.57079601e+00f, x);
+  r = fmaf(k, -3.13916473e-07f, r);
+  r = fmaf(k, -5.39030253e-15f, r);
+  const float s = r * r;
+  float z = 2.86567956e-6f;
+  z = fmaf(z, s, -1.98559923e-4f);
+  z = fmaf(z, s, 8.33338592e-3f);
+  z = fmaf(z, s, -1.66666672e-1f);
+  const float ps = fmaf(z, r * s, r);
+  z = 2.44677067e-5f;
+  z = fmaf(z, s, -1.38877297e-3f);
+  z = fmaf(z, s, 4.16666567e-2f);
+  z = fmaf(z, s, -5.0e-1f);
+  const float pc = fmaf(z, s, 1.0f);
+  const int i = (int)k;
+  float a = (i & 1) ? pc : ps, b = (i & 1) ? ps : pc;
+  if (i & 2) a = -a;
+  if ((i + 1) & 2) b = -b;
+  *sn = a;
+  *cs = b;
+}
+
 struct TgFrame {
   float r[9];  // row-major rotation
   float t[3];
@@ -34,7 +69,7 @@ __device__ __forceinline__ void tg_frame_child(const TgFrame& P, float ox, float
     return;
   }
   float s, c;
-  sincosf(q, &s, &c);
+  tg_sincos(q, &s, &c);
   // columns (a, b) that mix: x-axis -> (1,2), y-axis -> (2,0), z-axis -> (0,1)
   const int a = (kind == 2) ? 1 : (kind == 3) ? 2 : 0;
   const int b = (kind == 2) ? 2 : (kind == 3) ? 0 : 1;
@@ -66,7 +101,7 @@ struct TgBase {  // SE(2) base pose
 };
 __device__ __forceinline__ TgBase tg_base(float x, float y, float theta) {
   TgBase b;
-  sincosf(theta, &b.s, &b.c);
+  tg_sincos(theta, &b.s, &b.c);
   b.x = x;
   b.y = y;
   return b;

@@ -93,64 +93,64 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
   unsigned head = 0;  // ring positions count up; slot = position & (TGC_RING - 1)
   const unsigned lane = threadIdx.x & 31;
   const int ntiles = (B + TGC_BLOCK - 1) / TGC_BLOCK;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int i = tile * TGC_BLOCK + threadIdx.x;
-    const bool live = i < B;
+  // The loop body holds the only copy of stage A and stage B (the kernel is instruction-cache
+  // sensitive): the last, extra iteration (tile >= ntiles) only drains what is left in the ring.
+  for (int tile = blockIdx.x;; tile += gridDim.x) {
+    const bool last = tile >= ntiles;  // block-uniform
     float cfg[11];
-    TgClass cl;
-    tg_class_clear(cl);
-    if (live) {
-      cfg[0] = __ldg(base + 3 * (size_t)i); cfg[1] = __ldg(base + 3 * (size_t)i + 1); cfg[2] = __ldg(base + 3 * (size_t)i + 2);
-      if (!g.empty) {
-        const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
-        tg_stage_a(g, thr, p, cl);
+    if (!last) {
+      const int i = tile * TGC_BLOCK + threadIdx.x;
+      const bool live = i < B;
+      TgClass cl;
+      tg_class_clear(cl);
+      if (live) {
+        cfg[0] = __ldg(base + 3 * (size_t)i); cfg[1] = __ldg(base + 3 * (size_t)i + 1); cfg[2] = __ldg(base + 3 * (size_t)i + 2);
+        if (!g.empty) {
+          const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
+          tg_stage_a(g, thr, p, cl);
+        }
+        if (cl.collide) valid[i] = 0;
       }
-      if (cl.collide) valid[i] = 0;
-    }
-    const bool surv = live && !cl.collide;
-    const unsigned m = __ballot_sync(0xffffffffu, surv);
-    const unsigned ncol = __popc(__ballot_sync(0xffffffffu, live)) - __popc(m);
-    if (lane == 0 && ncol) atomicAdd(&ctr->definite_collisions, (unsigned long long)ncol);
-    if (m) {
-      unsigned pos = 0;
-      if (lane == 0) pos = atomicAdd(&s_tail, (unsigned)__popc(m));
-      pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
-      if (surv) {
-        const float4 a0 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i);
-        const float4 a1 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i + 1);
-        const unsigned sl = pos & (TGC_RING - 1);
-        ring.cfg[0][sl] = cfg[0]; ring.cfg[1][sl] = cfg[1]; ring.cfg[2][sl] = cfg[2];
-        ring.cfg[3][sl] = a0.x; ring.cfg[4][sl] = a0.y; ring.cfg[5][sl] = a0.z; ring.cfg[6][sl] = a0.w;
-        ring.cfg[7][sl] = a1.x; ring.cfg[8][sl] = a1.y; ring.cfg[9][sl] = a1.z; ring.cfg[10][sl] = a1.w;
-        ring.idx[sl] = (uint32_t)i;
-        ring.amb0[sl] = cl.amb[0];
+      const bool surv = live && !cl.collide;
+      const unsigned m = __ballot_sync(0xffffffffu, surv);
+      const unsigned ncol = __popc(__ballot_sync(0xffffffffu, live)) - __popc(m);
+      if (lane == 0 && ncol) atomicAdd(&ctr->definite_collisions, (unsigned long long)ncol);
+      if (m) {
+        unsigned pos = 0;
+        if (lane == 0) pos = atomicAdd(&s_tail, (unsigned)__popc(m));
+        pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
+        if (surv) {
+          const float4 a0 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i);
+          const float4 a1 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i + 1);
+          const unsigned sl = pos & (TGC_RING - 1);
+          ring.cfg[0][sl] = cfg[0]; ring.cfg[1][sl] = cfg[1]; ring.cfg[2][sl] = cfg[2];
+          ring.cfg[3][sl] = a0.x; ring.cfg[4][sl] = a0.y; ring.cfg[5][sl] = a0.z; ring.cfg[6][sl] = a0.w;
+          ring.cfg[7][sl] = a1.x; ring.cfg[8][sl] = a1.y; ring.cfg[9][sl] = a1.z; ring.cfg[10][sl] = a1.w;
+          ring.idx[sl] = (uint32_t)i;
+          ring.amb0[sl] = cl.amb[0];
+        }
       }
     }
     __syncthreads();
-    const bool run_b = (s_tail - head) >= TGC_BLOCK;  // uniform: s_tail is stable between the two barriers
+    const unsigned avail = s_tail - head;  // block-uniform: s_tail is stable between the two barriers; < 2 * TGC_BLOCK
+    const bool run_b = avail >= TGC_BLOCK || (last && avail != 0u);
+    const bool live_b = run_b && threadIdx.x < avail;
     uint32_t e_idx = 0, e_amb = 0;
-    if (run_b) {
+    if (run_b) {  // block-uniform
       const unsigned sl = (head + threadIdx.x) & (TGC_RING - 1);
 #pragma unroll
-      for (int k = 0; k < 11; ++k) cfg[k] = ring.cfg[k][sl];
-      e_idx = ring.idx[sl];
-      e_amb = ring.amb0[sl];
+      for (int k = 0; k < 11; ++k) cfg[k] = live_b ? ring.cfg[k][sl] : 0.f;
+      if (live_b) {
+        e_idx = ring.idx[sl];
+        e_amb = ring.amb0[sl];
+      }
     }
     __syncthreads();
     if (run_b) {
-      tg_stage_b_entry(g, thr, ex, cfg, e_idx, e_amb, valid, qu, ctr, true);
-      head += TGC_BLOCK;
+      tg_stage_b_entry(g, thr, ex, cfg, e_idx, e_amb, valid, qu, ctr, live_b);
+      head += min(avail, (unsigned)TGC_BLOCK);
     }
-  }
-  __syncthreads();
-  const unsigned left = s_tail - head;  // < TGC_BLOCK
-  if (left) {  // uniform
-    const bool live = threadIdx.x < left;
-    float cfg[11];
-    const unsigned sl = (head + threadIdx.x) & (TGC_RING - 1);
-#pragma unroll
-    for (int k = 0; k < 11; ++k) cfg[k] = live ? ring.cfg[k][sl] : 0.f;
-    tg_stage_b_entry(g, thr, ex, cfg, live ? ring.idx[sl] : 0u, live ? ring.amb0[sl] : 0u, valid, qu, ctr, live);
+    if (last) break;
   }
 }
 
@@ -194,6 +194,8 @@ __device__ __forceinline__ uint32_t tg_mask_range(const uint32_t* mask, int k0, 
 __global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueue qu, uint8_t* __restrict__ valid, TgCounters* ctr) {
   __shared__ float4 s_sph[TGR_CAP];
   __shared__ uint16_t s_own[TGR_CAP];
+  __shared__ uint8_t s_flag[TGR_CAP];
+  __shared__ uint32_t s_best[TGR_ITEMS];
   __shared__ uint32_t s_target[TGR_ITEMS];
   __shared__ uint8_t s_done[TGR_ITEMS];
   __shared__ int s_warp_tot[TGR_BLOCK / 32];
@@ -270,11 +272,67 @@ __global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueu
       }
       __syncthreads();
       const int nw = min(total - w0, TGR_CAP);
+#ifdef TG_STATS
+      if (threadIdx.x == 0) atomicAdd(&tg_stats[1], (unsigned long long)nw);
+#endif
+      // Step 2, one thread per listed sphere: re-read the sphere's distance code and tighten the
+      // bound with the exact offset e = |c - voxel centre| (phase 1 uses the worst case e = h):
+      //   k q - e - h  <=  dist(c, cloud)  <=  (k + 1) q + e + h.
+      // Definitely free spheres leave the list, a definitely colliding one settles its item, and
+      // the rest get a priority = estimated clearance; the item's most promising sphere is kept in
+      // s_best (packed priority | slot, smallest wins).
+      if (threadIdx.x < TGR_ITEMS) s_best[threadIdx.x] = 0xFFFFFFFFu;
+      __syncthreads();
+      for (int j = threadIdx.x; j < nw; j += TGR_BLOCK) {
+        const float4 c = s_sph[j];
+        const int own = s_own[j];
+        const float gx = c.x * g.vpm, gy = c.y * g.vpm, gz = c.z * g.vpm;
+        const float fx = fminf(fmaxf(gx + g.bias[0], TG_MAGIC), g.hi[0]);
+        const float fy = fminf(fmaxf(gy + g.bias[1], TG_MAGIC), g.hi[1]);
+        const float fz = fminf(fmaxf(gz + g.bias[2], TG_MAGIC), g.hi[2]);
+        const unsigned idx = __float_as_uint(fx) + (unsigned)g.nx * __float_as_uint(fy) + (unsigned)g.nxy * __float_as_uint(fz) - g.idx_bias;
+        const int k = (int)__ldg(g.df + idx);
+        const float ex = gx - (fx - g.bias[0]), ey = gy - (fy - g.bias[1]), ez = gz - (fz - g.bias[2]);
+        const float e = sqrtf(fmaf(ex, ex, fmaf(ey, ey, ez * ez))) / g.vpm;
+        const float hs = 0.5f * g.slack + 1e-5f;
+        const float lo = (float)k * g.q - e - hs;
+        const float hi = (float)(k + 1) * g.q + e + hs;
+        uint8_t flag = 0;
+        if (lo > c.w) {
+          flag = 1;  // definitely free
+        } else if (k < 255 && hi < c.w) {
+          flag = 1;  // definitely colliding: the item is settled
+          s_done[own] = 1;
+          valid[s_target[own]] = 0;
+        } else {
+          const float est = ((float)k + 0.5f) * g.q - c.w;  // estimated clearance, about [-0.1, 0.1] m
+          const int pr = min(max((int)((est + 0.1f) * 327675.0f), 0), 65535);
+          atomicMin(&s_best[own], ((unsigned)pr << 16) | (unsigned)j);
+        }
+        s_flag[j] = flag;
+      }
+      __syncthreads();
+      // Step 3a: the best sphere of every unsettled item first (nine items in ten end here)
+      for (int itx = (int)warp; itx < TGR_ITEMS; itx += TGR_BLOCK / 32) {
+        const unsigned bk = s_best[itx];
+        if (bk == 0xFFFFFFFFu || s_done[itx]) continue;  // warp-uniform
+        const float4 c = s_sph[bk & 0xFFFFu];
+        if (tg_warp_sphere_hits(g, c.x, c.y, c.z, c.w)) {
+          TG_STAT(8, 1);
+          if (lane == 0) {
+            s_done[itx] = 1;
+            valid[s_target[itx]] = 0;
+          }
+        }
+      }
+      __syncthreads();
+      // Step 3b: the remaining spheres of the items that are still open
       for (int j = (int)warp; j < nw; j += TGR_BLOCK / 32) {
         const int own = s_own[j];
-        if (s_done[own]) continue;  // warp-uniform
+        if (s_flag[j] || s_done[own] || (s_best[own] & 0xFFFFu) == (unsigned)j) continue;  // warp-uniform
         const float4 c = s_sph[j];
         if (tg_warp_sphere_hits(g, c.x, c.y, c.z, c.w)) {
+          TG_STAT(8, 1);
           if (lane == 0) {
             s_done[own] = 1;
             valid[s_target[own]] = 0;
@@ -560,6 +618,24 @@ extern "C" int tg_env_timing_read(tg_env* env, double* out3) {
   out3[2] = (double)(ev.size() / 3);
   for (cudaEvent_t e : ev) cudaEventDestroy(e);
   ev.clear();
+  return TG_OK;
+}
+
+// Debug statistics of the narrow phase (only filled by a -DTG_STATS build; zeros otherwise).
+extern "C" int tg_debug_stats(int64_t* out16, int reset) {
+  TG_CHECK_ARG(out16 != nullptr, "tg_debug_stats: out is NULL");
+#ifdef TG_STATS
+  unsigned long long h[16];
+  TG_CUDA(cudaMemcpyFromSymbol(h, tg_stats, sizeof(h)));
+  for (int i = 0; i < 16; ++i) out16[i] = (int64_t)h[i];
+  if (reset) {
+    memset(h, 0, sizeof(h));
+    TG_CUDA(cudaMemcpyToSymbol(tg_stats, h, sizeof(h)));
+  }
+#else
+  (void)reset;
+  for (int i = 0; i < 16; ++i) out16[i] = 0;
+#endif
   return TG_OK;
 }
 

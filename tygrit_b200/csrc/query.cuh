@@ -46,7 +46,7 @@ struct TgPose {
 };
 __device__ __forceinline__ TgPose tg_pose(const TgGrid& g, float bx, float by, float bth) {
   float s, c;
-  sincosf(bth, &s, &c);
+  tg_sincos(bth, &s, &c);
   TgPose p;
   p.cs = g.vpm * c;
   p.sn = g.vpm * s;
@@ -282,6 +282,13 @@ __device__ inline float tg_sphere_clearance(const TgGrid& g, float cx, float cy,
 // ranges of the 32 rows are then concatenated (warp prefix sum) and scanned together, 32 points per
 // step with coalesced float4 loads; the first hit ends the walk through __any_sync.
 // ------------------------------------------------------------------------------------------------
+#ifdef TG_STATS
+__device__ unsigned long long tg_stats[16];
+#define TG_STAT(i, v) do { if ((threadIdx.x & 31) == 0) atomicAdd(&tg_stats[i], (unsigned long long)(v)); } while (0)
+#else
+#define TG_STAT(i, v) do { } while (0)
+#endif
+
 struct TgRows {  // cell rows of a sphere's bounding box
   int z0, y0, ny, nrows;
   float inv_ny;
@@ -331,6 +338,8 @@ __device__ __forceinline__ bool tg_scan_ranges(const TgGrid& g, float cx, float 
     if ((int)lane >= o) incl += t;
   }
   const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+  TG_STAT(4, (total + 31) / 32);
+  TG_STAT(9, total);
   for (uint32_t j0 = 0; j0 < total; j0 += 32) {
     const uint32_t j = j0 + lane;
     int lo = 0;  // owner = first lane whose inclusive sum exceeds j (binary search over the warp's registers)
@@ -357,8 +366,11 @@ __device__ __forceinline__ bool tg_warp_sphere_hits(const TgGrid& g, float cx, f
   const unsigned lane = threadIdx.x & 31;
   const float Re = R + 1e-4f;
   const TgRows w = tg_rows(g, cy, cz, Re);
+  TG_STAT(2, 1);
+  TG_STAT(R < 0.13f ? 5 : (R < 0.2f ? 6 : 7), 1);
   for (int r0 = 0; r0 < w.nrows; r0 += 32) {
     uint32_t s, e;
+    TG_STAT(3, 1);
     tg_row_range(g, w, cx, cy, cz, Re, r0 + (int)lane, s, e);
     if (tg_scan_ranges(g, cx, cy, cz, R * R, s, e)) return true;
   }
@@ -375,7 +387,7 @@ __device__ __forceinline__ float4 tg_sphere_world(const TgFrame* L, const TgBase
 }
 
 // Sphere obstacles and end-effector attachment (vamp_preview.py:242-304), brute force, exact.
-__device__ inline bool tg_extras_hit(const TgGrid& g, const TgExtras& ex, const float* cfg /*x,y,th,q0..q7*/) {
+static __device__ __noinline__ bool tg_extras_hit(const TgGrid& g, const TgExtras& ex, const float* cfg /*x,y,th,q0..q7*/) {
   float q10[10];
 #pragma unroll
   for (int i = 0; i < 8; ++i) q10[i] = cfg[3 + i];
@@ -406,7 +418,7 @@ __device__ inline bool tg_extras_hit(const TgGrid& g, const TgExtras& ex, const 
 }
 
 // Resolve an item with one lane (queue-overflow fallback): exact test of every ambiguous sphere.
-__device__ inline bool tg_resolve_item(const TgGrid& g, const float* cfg, const uint32_t* mask) {
+static __device__ __noinline__ bool tg_resolve_item(const TgGrid& g, const float* cfg, const uint32_t* mask) {
   float q10[10];
 #pragma unroll
   for (int i = 0; i < 8; ++i) q10[i] = cfg[3 + i];

@@ -196,6 +196,55 @@ def test_host_api_matches_device_api_and_chunks(room):
     assert np.array_equal(dev, again)                                  # deterministic
 
 
+def _read_structure(w):
+    """Parse the structure blob header (csrc/common.cuh TgHeader/TgGrid) and return the df code grid."""
+    import struct
+
+    n = w.used_bytes()
+    blob = w.blob_view(n).cpu().numpy()
+    magic, used, off_df, off_cells, off_pts = struct.unpack_from("<5Q", blob, 0)
+    vpm, b0, b1, b2, h0, h1, h2 = struct.unpack_from("<7f", blob, 40)
+    nx, ny, nz, nxy = struct.unpack_from("<4i", blob, 68)
+    idx_bias, = struct.unpack_from("<I", blob, 84)
+    q, slack = struct.unpack_from("<2f", blob, 88)
+    window, = struct.unpack_from("<i", blob, 96)
+    df = blob[off_df:off_df + nx * ny * nz].reshape(nz, ny, nx)
+    return dict(vpm=np.float32(vpm), bias=np.array([b0, b1, b2], np.float32), n=(nx, ny, nz), q=q, slack=slack, W=window, df=df)
+
+
+@pytest.mark.parametrize("vpm", [50.0, 80.0])
+def test_distance_grid_codes_bit_exact_vs_scipy_edt(vpm):
+    """K1's truncated EDT (bitmask X pass, DPX add-min Y/Z passes) against scipy's exact transform:
+    every voxel code must be floor(sqrt(d2) * 255 / W) of the exact squared voxel-centre distance."""
+    from scipy import ndimage
+
+    rng = np.random.default_rng(5)
+    pts = np.concatenate([
+        synth.tabletop_cloud(6000),
+        rng.uniform([-0.4, -0.9, 0.1], [1.9, 0.9, 1.7], (300, 3)).astype(np.float32),   # isolated points in free space
+    ]).astype(np.float32)
+    w = CollisionWorld(max_points=1 << 16, voxels_per_metre=vpm)
+    w.build(_cuda(pts))
+    torch.cuda.synchronize()
+    st = _read_structure(w)
+    nx, ny, nz = st["n"]
+    W = st["W"]
+    assert W <= 31
+    # voxel of a point: round-to-nearest of fma(x, vpm, bias) - 2^23 (same as k_count); ties are measure zero
+    f = (pts.astype(np.float64) * np.float64(st["vpm"]) + st["bias"].astype(np.float64)).astype(np.float32)
+    idx = (f.astype(np.float64) - 8388608.0).astype(np.int64)
+    assert (idx >= 0).all() and (idx < np.array([nx, ny, nz])).all()
+    occ = np.zeros((nz, ny, nx), dtype=bool)
+    occ[idx[:, 2], idx[:, 1], idx[:, 0]] = True
+    d2 = np.rint(ndimage.distance_transform_edt(~occ) ** 2).astype(np.int64)
+    code = np.floor(np.sqrt(d2.astype(np.float32)) * (np.float32(255.0) / np.float32(W))).astype(np.int64)
+    want = np.where(d2 < W * W, np.minimum(code, 254), 255).astype(np.uint8)
+    got = st["df"]
+    bad = np.argwhere(got != want)
+    assert bad.shape[0] == 0, f"{bad.shape[0]} voxel codes differ, first {bad[:3]}: got {got[tuple(bad[0])]} want {want[tuple(bad[0])]}"
+    w.close()
+
+
 def test_structure_export_import(room):
     cloud, w, cc = room
     arm, base = synth.random_configs(20_000, seed=31)

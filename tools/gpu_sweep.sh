@@ -1,8 +1,7 @@
 #!/bin/bash
-# parameter sweep of the config-check bench (short runs, no e2e / cpu legs)
+# parameter sweep of the config-check bench (short runs, no e2e / cpu legs).  usage: tools/gpu_sweep.sh "<args1>" "<args2>" ...
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-for args in "--vpm 50" "--vpm 58" "--vpm 66" "--vpm 66 --cpm 25" "--vpm 80 --cpm 25" "--vpm 100 --cpm 25"; do
+for args in "$@"; do
   python bench.py --configs 16777216 --steps 3 --warmup 3 --no-e2e --no-cpu $args > gpurun_out/sweep.json 2> gpurun_out/sweep.err || tail -3 gpurun_out/sweep.err
   python - "$args" <<'PY'
 import json,sys

@@ -9,8 +9,8 @@
 //   k_count       per point: cell key, rank inside its cell (global atomic), mark its voxel
 //   k_scan_*      exclusive scan of the cell histogram -> cell_start
 //   k_scatter     counting-sort scatter into float4 points (x fastest key => rows are contiguous)
-//   k_edt_x/y/z   exact truncated Euclidean distance transform between voxel centres,
-//                 shared-memory tiles, quantised to one byte per voxel
+//   k_edt_xy/z    exact truncated Euclidean distance transform between voxel centres from an
+//                 occupancy bitmask, shared-memory tiles + DPX add-min, one byte per voxel
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(256) k_bounds(const float* __restrict__ xyz, i
 // per point: cell key + rank in cell; mark the df voxel.  Points that are not finite or fall
 // outside the grids are dropped (key = 0xFFFFFFFF) and counted.
 __global__ void __launch_bounds__(256)
-k_count(const float* __restrict__ xyz, int n, TgGrid g, uint8_t* __restrict__ occ, uint32_t* __restrict__ cell_count,
+k_count(const float* __restrict__ xyz, int n, TgGrid g, uint32_t* __restrict__ occ_bits, int nwx, uint32_t* __restrict__ cell_count,
         uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int* __restrict__ dropped) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -97,9 +97,9 @@ k_count(const float* __restrict__ xyz, int n, TgGrid g, uint8_t* __restrict__ oc
     const bool in_df = fx >= TG_MAGIC && fx <= g.hi[0] && fy >= TG_MAGIC && fy <= g.hi[1] && fz >= TG_MAGIC && fz <= g.hi[2];
     const bool in_cells = cx >= 0 && cx < g.cnx && cy >= 0 && cy < g.cny && cz >= 0 && cz < g.cnz;
     if (in_df && in_cells) {
-      const unsigned v = (unsigned)__float_as_int(fx) + (unsigned)g.nx * (unsigned)__float_as_int(fy) +
-                         (unsigned)g.nxy * (unsigned)__float_as_int(fz) - g.idx_bias;
-      occ[v] = 1;
+      const unsigned ix = __float_as_uint(fx) - TG_MAGIC_BITS, iy = __float_as_uint(fy) - TG_MAGIC_BITS,
+                     iz = __float_as_uint(fz) - TG_MAGIC_BITS;
+      atomicOr(&occ_bits[((size_t)iz * g.ny + iy) * nwx + (ix >> 5)], 1u << (ix & 31));
       k = (uint32_t)((cz * g.cny + cy) * g.cnx + cx);
       rank[i] = atomicAdd(&cell_count[k], 1u);
     }
@@ -195,80 +195,95 @@ k_scatter(const float* __restrict__ xyz, int n, const uint32_t* __restrict__ key
 }
 
 // ---- truncated exact EDT --------------------------------------------------------------------------
-// pass X: g1 = distance (voxels) to the nearest occupied voxel in the same x-row, 255 if none within W
-__global__ void __launch_bounds__(256) k_edt_x(const uint8_t* __restrict__ occ, uint8_t* __restrict__ g1, int nx, int rows, int W) {
-  extern __shared__ uint8_t srow[];  // 8 rows of nx bytes
-  const int r0 = blockIdx.x * 8;
-  for (int j = threadIdx.x; j < 8 * nx; j += 256) {
-    const int r = r0 + j / nx;
-    srow[j] = r < rows ? occ[(size_t)r0 * nx + j] : 0;
-  }
-  __syncthreads();
-  for (int j = threadIdx.x; j < 8 * nx; j += 256) {
-    const int rr = j / nx, x = j - rr * nx;
-    if (r0 + rr >= rows) break;
-    const uint8_t* row = srow + rr * nx;
-    int d = 255;
-    if (row[x]) d = 0;
-    else
-      for (int k = 1; k <= W; ++k) {
-        if ((x - k >= 0 && row[x - k]) || (x + k < nx && row[x + k])) { d = k; break; }
-      }
-    g1[(size_t)r0 * nx + j] = (uint8_t)d;
-  }
+// Exact Euclidean distance transform between voxel centres, truncated at W voxels, separable:
+//   X  nearest occupied voxel in the same x-row, straight from the occupancy BITMASK (funnel shift
+//      + clz/ffs: O(1) per voxel, no scan);
+//   Y  g2(y) = min_k gX(y+k)^2 + k^2   (fused with X: gX is never written to HBM);
+//   Z  d2(z) = min_k g2(z+k)  + k^2,  code = d2 >= W^2 ? 255 : floor(sqrt(d2) * 255 / W).
+// The min-plus taps run on packed u16x2 pairs (two adjacent x per thread) with the DPX instruction
+// VIADDMNMX.U16x2 (__viaddmin_u16x2): one shared-memory load + one instruction per tap per 2 voxels.
+// Squared distances stay below 2*31^2; TGE_SENT marks "nothing within W" and survives the adds.
+#define TGE_SENT 0x7FFFu
+#define TGE_SENT2 0x7FFF7FFFu
+#define TGE_SEG 96     // voxels along the pass axis per block (plus a halo of W on both sides)
+#define TGE_THREADS 256
+
+__device__ __forceinline__ unsigned tge_row_dist2(const uint32_t* __restrict__ row, int nwx, int x, int W) {
+  const int wi = x >> 5, sh = x & 31;
+  const uint32_t wm = wi > 0 ? __ldg(row + wi - 1) : 0u;
+  const uint32_t w0 = wi < nwx ? __ldg(row + wi) : 0u;
+  const uint32_t wp = wi + 1 < nwx ? __ldg(row + wi + 1) : 0u;
+  const uint32_t r32 = __funnelshift_r(w0, wp, sh);       // bit 0 = voxel x, bit j = x + j
+  const uint32_t l32 = __funnelshift_l(wm, w0, 31 - sh);  // bit 31 = voxel x, bit 31 - j = x - j
+  const int dr = r32 ? __ffs(r32) - 1 : 64;
+  const int dl = l32 ? __clz(l32) : 64;
+  const int d = min(dl, dr);
+  return d <= W ? (unsigned)(d * d) : TGE_SENT;
 }
 
-// pass Y: g2 = min_y' g1(y')^2 + (y-y')^2  (u16, 65535 = none)
-__global__ void __launch_bounds__(256) k_edt_y(const uint8_t* __restrict__ g1, uint16_t* __restrict__ g2, int nx, int ny, int W) {
-  extern __shared__ uint8_t tile[];  // [ny][32]
-  const int x0 = blockIdx.x * 32, z = blockIdx.y;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const size_t slab = (size_t)z * nx * ny;
-  for (int y = ty; y < ny; y += 8) tile[y * 32 + tx] = (x0 + tx < nx) ? g1[slab + (size_t)y * nx + x0 + tx] : 255;
-  __syncthreads();
-  if (x0 + tx >= nx) return;
-  for (int y = ty; y < ny; y += 8) {
-    const int v0 = tile[y * 32 + tx];
-    int best = v0 == 255 ? 65535 : v0 * v0;
-    for (int k = 1; k <= W; ++k) {
-      const int k2 = k * k;
-      if (k2 >= best) break;
-      if (y - k >= 0) {
-        const int v = tile[(y - k) * 32 + tx];
-        if (v != 255) best = min(best, v * v + k2);
-      }
-      if (y + k < ny) {
-        const int v = tile[(y + k) * 32 + tx];
-        if (v != 255) best = min(best, v * v + k2);
-      }
+__device__ __forceinline__ unsigned tge_taps(const uint32_t* __restrict__ col /* tile + r*32 + lane */, int W) {
+  unsigned best = col[0];
+#pragma unroll 4
+  for (int k = 1; k <= W; ++k) {
+    const unsigned k2 = (unsigned)(k * k) * 0x10001u;
+    best = __viaddmin_u16x2(col[-32 * k], k2, best);
+    best = __viaddmin_u16x2(col[32 * k], k2, best);
+  }
+  return __vminu2(best, TGE_SENT2);
+}
+
+// passes X + Y.  grid (ceil(nx/64), ceil(ny/TGE_SEG), nz); g2 is u16 [nz][ny][nxp], nxp even.
+__global__ void __launch_bounds__(TGE_THREADS)
+k_edt_xy(const uint32_t* __restrict__ bits, uint32_t* __restrict__ g2w, int nx, int nxp, int nwx, int ny, int W) {
+  extern __shared__ uint32_t tile[];  // [TGE_SEG + 2W][32] packed pairs
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int x = blockIdx.x * 64 + 2 * lane, y0 = blockIdx.y * TGE_SEG, z = blockIdx.z;
+  const int rows = min(TGE_SEG, ny - y0) + 2 * W;
+  for (int r = warp; r < rows; r += TGE_THREADS / 32) {
+    const int y = y0 - W + r;
+    unsigned v = TGE_SENT2;
+    if (y >= 0 && y < ny && x < nx) {
+      const uint32_t* row = bits + ((size_t)z * ny + y) * nwx;
+      const unsigned a = tge_row_dist2(row, nwx, x, W);
+      const unsigned b = (x + 1 < nx) ? tge_row_dist2(row, nwx, x + 1, W) : TGE_SENT;
+      v = a | (b << 16);
     }
-    g2[slab + (size_t)y * nx + x0 + tx] = (uint16_t)best;
+    tile[r * 32 + lane] = v;
+  }
+  __syncthreads();
+  if (x >= nxp) return;
+  for (int r = W + warp; r < rows - W; r += TGE_THREADS / 32) {
+    const int y = y0 - W + r;
+    g2w[(((size_t)z * ny + y) * nxp + x) >> 1] = tge_taps(tile + r * 32 + lane, W);
   }
 }
 
-// pass Z: d2 = min_z' g2(z') + (z-z')^2 ; code = d2 >= W^2 ? 255 : floor(sqrt(d2) * 255 / W)
-__global__ void __launch_bounds__(256)
-k_edt_z(const uint16_t* __restrict__ g2, uint8_t* __restrict__ df, int nx, int ny, int nz, int W) {
-  extern __shared__ uint16_t tilez[];  // [nz][32]
-  const int x0 = blockIdx.x * 32, y = blockIdx.y;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const size_t nxy = (size_t)nx * ny;
-  for (int z = ty; z < nz; z += 8) tilez[z * 32 + tx] = (x0 + tx < nx) ? g2[z * nxy + (size_t)y * nx + x0 + tx] : 65535;
-  __syncthreads();
-  if (x0 + tx >= nx) return;
+// pass Z + quantisation.  grid (ceil(nx/64), ny, ceil(nz/TGE_SEG)).
+__global__ void __launch_bounds__(TGE_THREADS)
+k_edt_z(const uint32_t* __restrict__ g2w, uint8_t* __restrict__ df, int nx, int nxp, int ny, int nz, int W) {
+  extern __shared__ uint32_t tile[];  // [TGE_SEG + 2W][32] packed pairs, then the code table
+  __shared__ uint8_t lut[1024];       // d2 -> code for d2 < W^2 (W <= 31)
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int x = blockIdx.x * 64 + 2 * lane, y = blockIdx.y, z0 = blockIdx.z * TGE_SEG;
+  const int rows = min(TGE_SEG, nz - z0) + 2 * W;
   const float scale = 255.0f / (float)W;
-  const int W2 = W * W;
-  for (int z = ty; z < nz; z += 8) {
-    int best = tilez[z * 32 + tx];
-    for (int k = 1; k <= W; ++k) {
-      const int k2 = k * k;
-      if (k2 >= best) break;
-      if (z - k >= 0) best = min(best, (int)tilez[(z - k) * 32 + tx] + k2);
-      if (z + k < nz) best = min(best, (int)tilez[(z + k) * 32 + tx] + k2);
-    }
-    int code = 255;
-    if (best < W2) code = min(254, (int)floorf(sqrtf((float)best) * scale));
-    df[z * nxy + (size_t)y * nx + x0 + tx] = (uint8_t)code;
+  for (int d2 = threadIdx.x; d2 < 1024; d2 += TGE_THREADS)
+    lut[d2] = d2 < W * W ? (uint8_t)min(254, (int)floorf(sqrtf((float)d2) * scale)) : (uint8_t)255;
+  for (int r = warp; r < rows; r += TGE_THREADS / 32) {
+    const int z = z0 - W + r;
+    unsigned v = TGE_SENT2;
+    if (z >= 0 && z < nz && x < nxp) v = __ldg(g2w + ((((size_t)z * ny + y) * nxp + x) >> 1));
+    tile[r * 32 + lane] = v;
+  }
+  __syncthreads();
+  if (x >= nx) return;
+  for (int r = W + warp; r < rows - W; r += TGE_THREADS / 32) {
+    const int z = z0 - W + r;
+    const unsigned best = tge_taps(tile + r * 32 + lane, W);
+    const unsigned lo = best & 0xFFFFu, hi = best >> 16;
+    uint8_t* out = df + ((size_t)z * ny + y) * nx + x;
+    out[0] = lo < 1024u ? lut[lo] : (uint8_t)255;
+    if (x + 1 < nx) out[1] = hi < 1024u ? lut[hi] : (uint8_t)255;
   }
 }
 
@@ -302,7 +317,7 @@ static bool tg_plan_grids(tg_env* env, const float lo[3], const float hi[3], TgG
   for (int it = 0; it < 64; ++it) {
     const double slack = sqrt(3.0) / vpm + kEpsFp;
     int W = (int)ceil((r_need + slack + 0.004) * vpm) + 1;
-    if (W > 32) {  // window too wide for the transform: the grid is finer than useful
+    if (W > 31) {  // window too wide for the transform: the grid is finer than useful
       vpm *= 0.9;
       continue;
     }
@@ -387,13 +402,13 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
   env->max_voxels = max_voxels > 0 ? max_voxels : (int64_t)64 << 20;
   env->max_cells = env->max_voxels / 4;
   env->vpm_requested = voxels_per_metre;
-  env->cpm_requested = voxels_per_metre * 0.5f;
+  env->cpm_requested = voxels_per_metre * 0.4f;  // 5 cm cells at the default 2 cm voxels (sweep in profiles/)
   env->r_pt = point_radius;
   env->blob_capacity = TG_HEADER_BYTES + align256(env->max_voxels) + align256(4 * (env->max_cells + 1)) +
                        align256(16 * (size_t)max_points) + 1024;
   TG_CUDA(cudaMalloc(&env->blob, env->blob_capacity));
   TG_CUDA(cudaMalloc(&env->g1, env->max_voxels));
-  TG_CUDA(cudaMalloc(&env->g2, 2 * env->max_voxels));
+  TG_CUDA(cudaMalloc(&env->g2, 2 * env->max_voxels + env->max_voxels / 8 + 4096));  // u16 [nz][ny][nxp], nxp = nx rounded up to even
   TG_CUDA(cudaMalloc(&env->cell_count, 4 * (env->max_cells + 1)));
   TG_CUDA(cudaMalloc(&env->rank, 4 * max_points));
   TG_CUDA(cudaMalloc(&env->key, 4 * max_points));
@@ -419,7 +434,6 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
   // empty world until the first build
   env->grid.empty = 1;
   env->grid.r_pt = point_radius;
-  TG_CUDA(cudaFuncSetAttribute(k_edt_z, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * 32 * 2));
   *out = env;
   return TG_OK;
 }
@@ -539,21 +553,24 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   uint32_t* cell_start = (uint32_t*)(env->blob + h->off_cells);
   float4* pts = (float4*)(env->blob + h->off_pts);
 
-  TG_CUDA(cudaMemsetAsync(df, 0, nvox, st));  // df doubles as the occupancy map until pass X has read it
+  const int nwx = (g.nx + 31) / 32, nxp = (g.nx + 1) & ~1;
+  uint32_t* occ_bits = (uint32_t*)env->g1;  // occupancy bitmask [nz][ny][nwx]
+  TG_CUDA(cudaMemsetAsync(occ_bits, 0, 4 * (size_t)g.nz * g.ny * nwx, st));
   TG_CUDA(cudaMemsetAsync(env->cell_count, 0, 4 * ((size_t)ncell + 1), st));
   TG_CUDA(cudaMemsetAsync(env->bounds_dev + 6, 0, sizeof(int), st));
-  k_count<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, g, df, env->cell_count, env->key, env->rank, env->bounds_dev + 6);
+  k_count<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, g, occ_bits, nwx, env->cell_count, env->key, env->rank, env->bounds_dev + 6);
   const int nb = tg_div_up(ncell, SCAN_ITEMS);
   k_scan_block_sums<<<nb, 256, 0, st>>>(env->cell_count, ncell, env->scan_tmp);
   k_scan_sums<<<1, 1024, 0, st>>>(env->scan_tmp, nb);
   k_scan_apply<<<nb, 256, 0, st>>>(env->cell_count, ncell, env->scan_tmp, cell_start);
   k_scatter<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, env->key, env->rank, cell_start, pts);
-  const int rows = g.ny * g.nz;
-  k_edt_x<<<tg_div_up(rows, 8), 256, 8 * g.nx, st>>>(df, env->g1, g.nx, rows, g.window);
-  k_edt_y<<<dim3(tg_div_up(g.nx, 32), g.nz), 256, g.ny * 32, st>>>(env->g1, env->g2, g.nx, g.ny, g.window);
-  k_edt_z<<<dim3(tg_div_up(g.nx, 32), g.ny), 256, g.nz * 32 * 2, st>>>(env->g2, df, g.nx, g.ny, g.nz, g.window);
+  const size_t tile_bytes = (size_t)(TGE_SEG + 2 * g.window) * 32 * sizeof(uint32_t);
+  k_edt_xy<<<dim3(tg_div_up(nxp, 64), tg_div_up(g.ny, TGE_SEG), g.nz), TGE_THREADS, tile_bytes, st>>>(
+      occ_bits, (uint32_t*)env->g2, g.nx, nxp, nwx, g.ny, g.window);
+  k_edt_z<<<dim3(tg_div_up(g.nx, 64), g.ny, tg_div_up(g.nz, TGE_SEG)), TGE_THREADS, tile_bytes, st>>>(
+      (const uint32_t*)env->g2, df, g.nx, nxp, g.ny, g.nz, g.window);
   TG_CUDA(cudaGetLastError());
-  env->launches += 8;
+  env->launches += 7;
 
   tg_compute_thresholds(g, &env->thr);
   env->grid = g;

@@ -165,6 +165,7 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
 #define TGR_BLOCK 128   // threads per block
 #define TGR_ITEMS 64    // queue items per batch: small batches keep the serial sphere chain per warp short
 #define TGR_CAP 1024    // sphere-list slots per pass
+#define TGR_ROUNDS 1    // best-first rounds before the rest of the list is walked in order
 
 __device__ __forceinline__ void tg_emit_frame(const TgFrame& F, const TgBase& b, float r_pt, uint32_t bits, int k_base,
                                               int& ord, int w0, float4* __restrict__ s_sph, uint16_t* __restrict__ s_own) {
@@ -194,7 +195,7 @@ __device__ __forceinline__ uint32_t tg_mask_range(const uint32_t* mask, int k0, 
 __global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueue qu, uint8_t* __restrict__ valid, TgCounters* ctr) {
   __shared__ float4 s_sph[TGR_CAP];
   __shared__ uint16_t s_own[TGR_CAP];
-  __shared__ uint8_t s_flag[TGR_CAP];
+  __shared__ uint32_t s_key[TGR_CAP];
   __shared__ uint32_t s_best[TGR_ITEMS];
   __shared__ uint32_t s_target[TGR_ITEMS];
   __shared__ uint8_t s_done[TGR_ITEMS];
@@ -281,8 +282,6 @@ __global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueu
       // Definitely free spheres leave the list, a definitely colliding one settles its item, and
       // the rest get a priority = estimated clearance; the item's most promising sphere is kept in
       // s_best (packed priority | slot, smallest wins).
-      if (threadIdx.x < TGR_ITEMS) s_best[threadIdx.x] = 0xFFFFFFFFu;
-      __syncthreads();
       for (int j = threadIdx.x; j < nw; j += TGR_BLOCK) {
         const float4 c = s_sph[j];
         const int own = s_own[j];
@@ -293,43 +292,56 @@ __global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueu
         const unsigned idx = __float_as_uint(fx) + (unsigned)g.nx * __float_as_uint(fy) + (unsigned)g.nxy * __float_as_uint(fz) - g.idx_bias;
         const int k = (int)__ldg(g.df + idx);
         const float ex = gx - (fx - g.bias[0]), ey = gy - (fy - g.bias[1]), ez = gz - (fz - g.bias[2]);
-        const float e = sqrtf(fmaf(ex, ex, fmaf(ey, ey, ez * ez))) / g.vpm;
-        const float hs = 0.5f * g.slack + 1e-5f;
-        const float lo = (float)k * g.q - e - hs;
-        const float hi = (float)(k + 1) * g.q + e + hs;
-        uint8_t flag = 0;
+        const float eh = sqrtf(fmaf(ex, ex, fmaf(ey, ey, ez * ez))) / g.vpm + 0.5f * g.slack + 1e-5f;  // e + h
+        const float lo = (float)k * g.q - eh;
+        const float hi = (float)(k + 1) * g.q + eh;
+        uint32_t key = 0xFFFFFFFFu;  // not to be walked
         if (lo > c.w) {
-          flag = 1;  // definitely free
-        } else if (k < 255 && hi < c.w) {
-          flag = 1;  // definitely colliding: the item is settled
+          // definitely free
+        } else if (k < 255 && hi < c.w) {  // definitely colliding: the item is settled
           s_done[own] = 1;
           valid[s_target[own]] = 0;
         } else {
-          const float est = ((float)k + 0.5f) * g.q - c.w;  // estimated clearance, about [-0.1, 0.1] m
-          const int pr = min(max((int)((est + 0.1f) * 327675.0f), 0), 65535);
-          atomicMin(&s_best[own], ((unsigned)pr << 16) | (unsigned)j);
+          // position of R inside [lo, hi]: 0 = R at hi, certainly colliding; 1 = R at lo, certainly free
+          const float pos = __fdividef(hi - c.w, hi - lo);
+          const int pr = min(max((int)(pos * 65535.0f), 0), 65535);
+          key = ((unsigned)pr << 16) | (unsigned)j;
         }
-        s_flag[j] = flag;
+        s_key[j] = key;
       }
-      __syncthreads();
-      // Step 3a: the best sphere of every unsettled item first (nine items in ten end here)
-      for (int itx = (int)warp; itx < TGR_ITEMS; itx += TGR_BLOCK / 32) {
-        const unsigned bk = s_best[itx];
-        if (bk == 0xFFFFFFFFu || s_done[itx]) continue;  // warp-uniform
-        const float4 c = s_sph[bk & 0xFFFFu];
-        if (tg_warp_sphere_hits(g, c.x, c.y, c.z, c.w)) {
-          TG_STAT(8, 1);
+      // Step 3a: best-first rounds.  Every round picks, per open item, the listed sphere most likely
+      // to collide (smallest key) and walks it; nine items in ten are settled within two rounds.
+      for (int round = 0; round < TGR_ROUNDS; ++round) {
+        if (threadIdx.x < TGR_ITEMS) s_best[threadIdx.x] = 0xFFFFFFFFu;
+        __syncthreads();
+        for (int j = threadIdx.x; j < nw; j += TGR_BLOCK) {
+          const uint32_t key = s_key[j];
+          if (key != 0xFFFFFFFFu && !s_done[s_own[j]]) atomicMin(&s_best[s_own[j]], key);
+        }
+        __syncthreads();
+        bool any = false;
+        for (int itx = (int)warp; itx < TGR_ITEMS; itx += TGR_BLOCK / 32) {
+          const unsigned bk = s_best[itx];
+          if (bk == 0xFFFFFFFFu) continue;  // warp-uniform
+          any = true;
+          const unsigned slot = bk & 0xFFFFu;
+          const float4 c = s_sph[slot];
+          const bool hit = tg_warp_sphere_hits(g, c.x, c.y, c.z, c.w);
+          if (hit) TG_STAT(8, 1);
           if (lane == 0) {
-            s_done[itx] = 1;
-            valid[s_target[itx]] = 0;
+            s_key[slot] = 0xFFFFFFFFu;
+            if (hit) {
+              s_done[itx] = 1;
+              valid[s_target[itx]] = 0;
+            }
           }
         }
+        if (!__syncthreads_or(any)) break;
       }
-      __syncthreads();
       // Step 3b: the remaining spheres of the items that are still open
       for (int j = (int)warp; j < nw; j += TGR_BLOCK / 32) {
         const int own = s_own[j];
-        if (s_flag[j] || s_done[own] || (s_best[own] & 0xFFFFu) == (unsigned)j) continue;  // warp-uniform
+        if (s_key[j] == 0xFFFFFFFFu || s_done[own]) continue;  // warp-uniform
         const float4 c = s_sph[j];
         if (tg_warp_sphere_hits(g, c.x, c.y, c.z, c.w)) {
           TG_STAT(8, 1);

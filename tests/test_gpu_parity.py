@@ -391,6 +391,32 @@ def test_self_filter_depth_batch_vs_oracle():
             assert not mask[s][~keep].any()                             # invalid depth is never kept
             n_removed += int((signed < 0).sum())
         assert n_removed > 50                                           # the robot was really in view
+        if stride == 1:   # the tile-culled fast path (mask only) must give the generic kernel's mask, byte for byte
+            fast = engine.self_filter_depth(_cuda(depth), K, _cuda(states), 0.08, (0.2, 3.0), 1).cpu().numpy().astype(bool)
+            assert np.array_equal(fast, mask)
+
+
+@pytest.mark.parametrize("shape", [(480, 640), (100, 164)])
+def test_self_filter_fast_path_equals_generic_kernel(shape):
+    """Full-resolution frames (and a size with ragged tiles): k_self_filter_tiles vs k_self_filter_depth."""
+    H, W = shape
+    K = synth.HEAD_CAMERA_K.copy()
+    K[:2] *= W / 640.0
+    states = synth.random_states(24, seed=21)
+    states[::2, 12] = 0.9                                             # half of the states look down at the arm
+    st = _cuda(states)
+    bx = _cuda(np.array([[*lo, *hi] for lo, hi in synth.room_boxes()], np.float32))
+    depth = torch.empty(len(states), H, W, device="cuda")
+    from tygrit_b200 import _native as N
+    N.check(N.lib().tg_synth_depth(st.data_ptr(), len(states), bx.data_ptr(), bx.shape[0], H, W, np.ascontiguousarray(K).ctypes.data,
+                                   0.0, 3, depth.data_ptr(), None), "tg_synth_depth")
+    depth[1, 5, 7] = float("nan")
+    depth[2, 9, 11] = float("inf")
+    slow, _ = engine.self_filter_depth(depth, K, st, 0.08, (0.2, 3.0), 1, want_world=True)
+    fast = engine.self_filter_depth(depth, K, st, 0.08, (0.2, 3.0), 1)
+    assert torch.equal(fast, slow)
+    removed = ((depth > 0.2) & (depth < 3.0) & (slow == 0)).float().mean().item()
+    assert removed > 1e-3                                             # robot pixels exist in these frames
 
 
 def test_synth_depth_kernel_matches_numpy_twin():

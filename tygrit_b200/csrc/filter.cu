@@ -20,6 +20,7 @@ struct TgFilterState {  // per robot state, produced by k_filter_prepare
   float cam_t[3];
   float lo[3], hi[3];   // bounding box of the sphere centres
   float c[TGM_N_SPHERES * 3];
+  float cc[TGM_N_SPHERES * 3];  // the same centres in the camera frame (cull tests only, never the verdict)
 };
 
 __device__ __forceinline__ bool tg_inside_any(const float* __restrict__ c, int S, float px, float py, float pz, float r2) {
@@ -121,6 +122,11 @@ __global__ void __launch_bounds__(128) k_filter_prepare(const float* __restrict_
     o.cam_r[3 * r + 1] = -Rw[3 * r + 2];
     o.cam_r[3 * r + 2] = Rw[3 * r + 0];
   }
+  for (int j = 0; j < TGM_N_SPHERES; ++j) {  // c_cam = R^T (c_world - t)
+    const float dx = o.c[3 * j] - o.cam_t[0], dy = o.c[3 * j + 1] - o.cam_t[1], dz = o.c[3 * j + 2] - o.cam_t[2];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) o.cc[3 * j + a] = fmaf(o.cam_r[a], dx, fmaf(o.cam_r[3 + a], dy, o.cam_r[6 + a] * dz));
+  }
 }
 
 struct TgDepthParams {
@@ -197,6 +203,130 @@ k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __rest
   }
 }
 
+// ---- fast path: full-resolution frames, mask only ---------------------------------------------
+// One warp = one 32 x 16 pixel tile (lane = 4 consecutive pixels x 4 rows, 128-bit depth loads, 32-bit
+// mask stores).  The warp first finds the spheres that can touch the tile at all: a sphere at camera-
+// frame (X, Y, Z) can only contain back-projected points with depth in [Z - r, Z + r] whose image
+// position lies in its projected box (conservative, 2 mm margin; 4 spheres per lane + ballot).  For
+// almost every tile that set is empty and a pixel costs one load, three compares and a quarter of a
+// store — the kernel then runs at HBM speed.  Pixels of the remaining tiles whose depth falls into a
+// candidate's depth interval are transformed and tested exactly as in k_self_filter_depth (same
+// rounding, same verdict).
+#define TGT_W 32
+#define TGT_H 16
+
+__global__ void __launch_bounds__(TGF_BLOCK)
+k_self_filter_tiles(const float* __restrict__ depth, const TgFilterState* __restrict__ prep, TgDepthParams p, float radius,
+                    uint8_t* __restrict__ mask) {
+  __shared__ TgFilterState st;
+  const int s = blockIdx.y;
+  {
+    const float* src = reinterpret_cast<const float*>(prep + s);
+    float* dst = reinterpret_cast<float*>(&st);
+    for (int j = threadIdx.x; j < (int)(sizeof(TgFilterState) / 4); j += TGF_BLOCK) dst[j] = src[j];
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tiles_x = (p.W + TGT_W - 1) / TGT_W, tiles_y = (p.H + TGT_H - 1) / TGT_H;
+  const int tile = blockIdx.x * (TGF_BLOCK / 32) + warp;
+  if (tile >= tiles_x * tiles_y) return;
+  const int ty0 = tile / tiles_x, tx0 = tile - ty0 * tiles_x;
+  const int u0 = tx0 * TGT_W, v0 = ty0 * TGT_H;
+  // candidate spheres of the tile
+  const float rp = radius + 2e-3f;
+  const float ifx = (float)(1.0 / p.fx), ify = (float)(1.0 / p.fy), cxf = (float)p.cx, cyf = (float)p.cy;
+  const float a0 = ((float)u0 - 0.5f - cxf) * ifx, a1 = ((float)(u0 + TGT_W) - 0.5f - cxf) * ifx;
+  const float b0 = ((float)v0 - 0.5f - cyf) * ify, b1 = ((float)(v0 + TGT_H) - 0.5f - cyf) * ify;
+  uint32_t m[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int j = lane + 32 * q;
+    bool c = false;
+    if (j < TGM_N_SPHERES) {
+      const float X = st.cc[3 * j], Y = st.cc[3 * j + 1], Z = st.cc[3 * j + 2];
+      const float zl = fmaxf(fmaxf(Z - rp, p.zmin - 1e-3f), 0.f), zh = fminf(Z + rp, p.zmax + 1e-3f);
+      if (zl <= zh) {
+        const float xmin = (a0 >= 0.f ? zl : zh) * a0, xmax = (a1 >= 0.f ? zh : zl) * a1;
+        const float ymin = (b0 >= 0.f ? zl : zh) * b0, ymax = (b1 >= 0.f ? zh : zl) * b1;
+        c = xmin <= X + rp && xmax >= X - rp && ymin <= Y + rp && ymax >= Y - rp;
+      }
+    }
+    m[q] = __ballot_sync(0xffffffffu, c);
+  }
+  // depth of this lane's 16 pixels
+  const int tx = lane & 7, tyy = lane >> 3;
+  const int u = u0 + 4 * tx;
+  const float* img = depth + (size_t)s * p.H * p.W;
+  float z[16];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int v = v0 + tyy + 4 * j;
+    float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (v < p.H && u < p.W) d = __ldg(reinterpret_cast<const float4*>(img + (size_t)v * p.W + u));
+    z[4 * j] = d.x; z[4 * j + 1] = d.y; z[4 * j + 2] = d.z; z[4 * j + 3] = d.w;
+  }
+  uint32_t ok = 0;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    float zz = z[k];
+    if (isnan(zz)) zz = 0.f;  // np.nan_to_num; +-inf become +-FLT_MAX, which the range test rejects like the reference
+    else if (isinf(zz)) zz = zz > 0 ? 3.4028234663852886e38f : -3.4028234663852886e38f;
+    z[k] = zz;
+    if (zz > 0.f && zz >= p.zmin && zz <= p.zmax) ok |= 1u << k;
+  }
+  if ((m[0] | m[1] | m[2] | m[3]) != 0u) {  // warp-uniform: the robot may be visible in this tile
+    uint32_t cand = 0;  // pixels whose depth lies in some candidate sphere's depth interval
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t bits = m[q];
+      while (bits) {
+        const int j = 32 * q + __ffs(bits) - 1;
+        bits &= bits - 1;
+        const float Z = st.cc[3 * j + 2];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) cand |= (fabsf(z[k] - Z) < rp ? 1u : 0u) << k;
+      }
+    }
+    cand &= ok;
+    while (cand) {  // rare: exact transform + exact test, same arithmetic as the generic kernel
+      const int k = __ffs(cand) - 1;
+      cand &= cand - 1;
+      const int uu = u + (k & 3), vv = v0 + tyy + 4 * (k >> 2);
+      float zz = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < 16; ++kk)
+        if (kk == k) zz = z[kk];  // register select: keeps z[] out of local memory
+      const float xc = (float)((((double)(float)uu - p.cx) * (double)zz) / p.fx);
+      const float yc = (float)((((double)(float)vv - p.cy) * (double)zz) / p.fy);
+      const float wx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[0]), __fmul_rn(yc, st.cam_r[1])), __fmul_rn(zz, st.cam_r[2])), st.cam_t[0]);
+      const float wy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[3]), __fmul_rn(yc, st.cam_r[4])), __fmul_rn(zz, st.cam_r[5])), st.cam_t[1]);
+      const float wz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[6]), __fmul_rn(yc, st.cam_r[7])), __fmul_rn(zz, st.cam_r[8])), st.cam_t[2]);
+      bool inside = false;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint32_t bits = m[q];
+        while (bits) {
+          const int j = 32 * q + __ffs(bits) - 1;
+          bits &= bits - 1;
+          const float dx = __fsub_rn(wx, st.c[3 * j]), dy = __fsub_rn(wy, st.c[3 * j + 1]), dz = __fsub_rn(wz, st.c[3 * j + 2]);
+          const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+          inside |= d2 < p.r2;
+        }
+      }
+      if (inside) ok &= ~(1u << k);
+    }
+  }
+  uint8_t* mrow = mask + (size_t)s * p.H * p.W;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int v = v0 + tyy + 4 * j;
+    if (v < p.H && u < p.W) {
+      const uint32_t b = (ok >> (4 * j)) & 0xFu;
+      *reinterpret_cast<uint32_t*>(mrow + (size_t)v * p.W + u) = (b & 1u) | ((b & 2u) << 7) | ((b & 4u) << 14) | ((b & 8u) << 21);
+    }
+  }
+}
+
 extern "C" int tg_self_filter_depth(const float* depth, int H, int W, int stride, const double* K, const float* states, int64_t S,
                                     float radius, float zmin, float zmax, uint8_t* mask, float* world, void* stream_) {
   TG_CHECK_ARG(H > 0 && W > 0 && stride >= 1 && S >= 0 && S < 65536, "tg_self_filter_depth: bad shape (S < 65536)");
@@ -217,8 +347,14 @@ extern "C" int tg_self_filter_depth(const float* depth, int H, int W, int stride
   TG_CUDA(cudaMallocAsync(&prep, sizeof(TgFilterState) * (size_t)S, st));
   k_filter_prepare<<<tg_div_up(S, 128), 128, 0, st>>>(states, (int)S, radius, prep);
   const int npx = p.Hs * p.Ws;
-  dim3 grid(tg_div_up(npx, TGF_BLOCK * 4), (unsigned)S);
-  k_self_filter_depth<4><<<grid, TGF_BLOCK, 0, st>>>(depth, prep, p, mask, world);
+  if (stride == 1 && world == nullptr && (W & 3) == 0 && ((uintptr_t)mask & 3) == 0) {
+    const int tiles = tg_div_up(W, TGT_W) * tg_div_up(H, TGT_H);
+    dim3 grid(tg_div_up(tiles, TGF_BLOCK / 32), (unsigned)S);
+    k_self_filter_tiles<<<grid, TGF_BLOCK, 0, st>>>(depth, prep, p, radius, mask);
+  } else {
+    dim3 grid(tg_div_up(npx, TGF_BLOCK * 4), (unsigned)S);
+    k_self_filter_depth<4><<<grid, TGF_BLOCK, 0, st>>>(depth, prep, p, mask, world);
+  }
   TG_CUDA(cudaGetLastError());
   TG_CUDA(cudaFreeAsync(prep, st));
   return TG_OK;

@@ -21,6 +21,7 @@ struct TgFilterState {  // per robot state, produced by k_filter_prepare
   float lo[3], hi[3];   // bounding box of the sphere centres
   float c[TGM_N_SPHERES * 3];
   float cc[TGM_N_SPHERES * 3];  // the same centres in the camera frame (cull tests only, never the verdict)
+  float img_box[4];             // conservative pixel box (u0, v0, u1, v1) of every sphere that can be seen at all
 };
 
 __device__ __forceinline__ bool tg_inside_any(const float* __restrict__ c, int S, float px, float py, float pz, float r2) {
@@ -77,63 +78,108 @@ extern "C" int tg_filter_points(const float* points, int64_t N, const float* cen
 }
 
 // ---- batched depth self-filter --------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_filter_prepare(const float* __restrict__ states, int S, float radius, TgFilterState* __restrict__ out) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= S) return;
-  const float* st = states + 13 * (size_t)s;
-  float q[10];
-#pragma unroll
-  for (int k = 0; k < 10; ++k) q[k] = st[3 + k];
-  TgFrame L[TGM_N_LINKS];
-  tg_fk_links(q, L);
-  const TgBase b = tg_base(st[0], st[1], st[2]);
-  TgFilterState& o = out[s];
-  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-  for (int j = 0; j < TGM_N_SPHERES; ++j) {
-    const float4 l = TGM_SPH_REF[j];
-    const float3 pb = tg_frame_apply(L[TGM_SPH_LINK[j]], l.x, l.y, l.z);
-    const float3 pw = tg_to_world(b, pb.x, pb.y, pb.z);
-    o.c[3 * j] = pw.x; o.c[3 * j + 1] = pw.y; o.c[3 * j + 2] = pw.z;
-    lo[0] = fminf(lo[0], pw.x); hi[0] = fmaxf(hi[0], pw.x);
-    lo[1] = fminf(lo[1], pw.y); hi[1] = fmaxf(hi[1], pw.y);
-    lo[2] = fminf(lo[2], pw.z); hi[2] = fmaxf(hi[2], pw.z);
-  }
-#pragma unroll
-  for (int a = 0; a < 3; ++a) {
-    o.lo[a] = lo[a] - radius - 1e-3f;
-    o.hi[a] = hi[a] + radius + 1e-3f;
-  }
-  // cam2world = SE2(base) * T(head_tilt) * Trans(cam offset) * R_cv->link   (camera.py:25-58)
-  const TgFrame& Tt = L[TGM_HEAD_TILT_LINK];
-  const float3 cb = tg_frame_apply(Tt, TGM_HEAD_CAMERA_OFF[0], TGM_HEAD_CAMERA_OFF[1], TGM_HEAD_CAMERA_OFF[2]);
-  const float3 cw = tg_to_world(b, cb.x, cb.y, cb.z);
-  o.cam_t[0] = cw.x; o.cam_t[1] = cw.y; o.cam_t[2] = cw.z;
-  // world rotation of head_tilt: Rz(theta) * R ; then columns: cv x -> -link y, cv y -> -link z, cv z -> link x
-  float Rw[9];
-#pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    Rw[c] = fmaf(b.c, Tt.r[c], -b.s * Tt.r[3 + c]);
-    Rw[3 + c] = fmaf(b.s, Tt.r[c], b.c * Tt.r[3 + c]);
-    Rw[6 + c] = Tt.r[6 + c];
-  }
-#pragma unroll
-  for (int r = 0; r < 3; ++r) {
-    o.cam_r[3 * r + 0] = -Rw[3 * r + 1];
-    o.cam_r[3 * r + 1] = -Rw[3 * r + 2];
-    o.cam_r[3 * r + 2] = Rw[3 * r + 0];
-  }
-  for (int j = 0; j < TGM_N_SPHERES; ++j) {  // c_cam = R^T (c_world - t)
-    const float dx = o.c[3 * j] - o.cam_t[0], dy = o.c[3 * j + 1] - o.cam_t[1], dz = o.c[3 * j + 2] - o.cam_t[2];
-#pragma unroll
-    for (int a = 0; a < 3; ++a) o.cc[3 * j + a] = fmaf(o.cam_r[a], dx, fmaf(o.cam_r[3 + a], dy, o.cam_r[6 + a] * dz));
-  }
-}
-
 struct TgDepthParams {
   int H, W, stride, Hs, Ws;
   double fx, fy, cx, cy;  // intrinsics of the decimated image (K rows 0,1 divided by stride in f64)
   float zmin, zmax, r2;
 };
+
+// One warp per robot state: lane 0 runs the FK chain and the camera pose, then the lanes share the
+// 111 spheres (world centres, camera-frame centres, bounding boxes).
+__global__ void __launch_bounds__(128)
+k_filter_prepare(const float* __restrict__ states, int S, float radius, TgDepthParams p, TgFilterState* __restrict__ out) {
+  __shared__ TgFrame sL[4][TGM_N_LINKS];
+  __shared__ TgBase sB[4];
+  __shared__ float sCam[4][12];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int s = blockIdx.x * 4 + w;
+  if (s >= S) return;  // warp-uniform
+  TgFilterState& o = out[s];
+  if (lane == 0) {
+    const float* st = states + 13 * (size_t)s;
+    float q[10];
+#pragma unroll
+    for (int k = 0; k < 10; ++k) q[k] = st[3 + k];
+    tg_fk_links(q, sL[w]);
+    const TgBase b = tg_base(st[0], st[1], st[2]);
+    sB[w] = b;
+    // cam2world = SE2(base) * T(head_tilt) * Trans(cam offset) * R_cv->link   (camera.py:25-58)
+    const TgFrame& Tt = sL[w][TGM_HEAD_TILT_LINK];
+    const float3 cb = tg_frame_apply(Tt, TGM_HEAD_CAMERA_OFF[0], TGM_HEAD_CAMERA_OFF[1], TGM_HEAD_CAMERA_OFF[2]);
+    const float3 cw = tg_to_world(b, cb.x, cb.y, cb.z);
+    sCam[w][9] = cw.x; sCam[w][10] = cw.y; sCam[w][11] = cw.z;
+    // world rotation of head_tilt: Rz(theta) * R ; then columns: cv x -> -link y, cv y -> -link z, cv z -> link x
+    float Rw[9];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      Rw[c] = fmaf(b.c, Tt.r[c], -b.s * Tt.r[3 + c]);
+      Rw[3 + c] = fmaf(b.s, Tt.r[c], b.c * Tt.r[3 + c]);
+      Rw[6 + c] = Tt.r[6 + c];
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      sCam[w][3 * r + 0] = -Rw[3 * r + 1];
+      sCam[w][3 * r + 1] = -Rw[3 * r + 2];
+      sCam[w][3 * r + 2] = Rw[3 * r + 0];
+    }
+  }
+  __syncwarp();
+  if (lane < 9) o.cam_r[lane] = sCam[w][lane];
+  else if (lane < 12) o.cam_t[lane - 9] = sCam[w][lane];
+  const float* R = sCam[w];
+  const float* t = sCam[w] + 9;
+  const TgBase b = sB[w];
+  const float rp = radius + 2e-3f;
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  float ib[4] = {INFINITY, INFINITY, -INFINITY, -INFINITY};
+  for (int j = lane; j < TGM_N_SPHERES; j += 32) {
+    const float4 l = TGM_SPH_REF[j];
+    const float3 pb = tg_frame_apply(sL[w][TGM_SPH_LINK[j]], l.x, l.y, l.z);
+    const float3 pw = tg_to_world(b, pb.x, pb.y, pb.z);
+    o.c[3 * j] = pw.x; o.c[3 * j + 1] = pw.y; o.c[3 * j + 2] = pw.z;
+    lo[0] = fminf(lo[0], pw.x); hi[0] = fmaxf(hi[0], pw.x);
+    lo[1] = fminf(lo[1], pw.y); hi[1] = fmaxf(hi[1], pw.y);
+    lo[2] = fminf(lo[2], pw.z); hi[2] = fmaxf(hi[2], pw.z);
+    // camera frame: c_cam = R^T (c_world - t)
+    const float dx = pw.x - t[0], dy = pw.y - t[1], dz = pw.z - t[2];
+    float cc[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) cc[a] = fmaf(R[a], dx, fmaf(R[3 + a], dy, R[6 + a] * dz));
+    o.cc[3 * j] = cc[0]; o.cc[3 * j + 1] = cc[1]; o.cc[3 * j + 2] = cc[2];
+    // pixel box of everything this sphere can contain: depth in [zl, zh], |x - X| < rp, |y - Y| < rp
+    const float zl = fmaxf(cc[2] - rp, p.zmin - 1e-3f), zh = fminf(cc[2] + rp, p.zmax + 1e-3f);
+    if (zl <= zh && zh > 0.f) {
+      if (zl < 0.01f) {  // reaches the camera: no useful bound
+        ib[0] = ib[1] = -INFINITY;
+        ib[2] = ib[3] = INFINITY;
+      } else {
+        const float fx = (float)p.fx, fy = (float)p.fy, cx = (float)p.cx, cy = (float)p.cy;
+        const float xa = cc[0] - rp, xb = cc[0] + rp, ya = cc[1] - rp, yb = cc[1] + rp;
+        ib[0] = fminf(ib[0], cx + fx * (xa >= 0.f ? xa / zh : xa / zl) - 1.5f);
+        ib[2] = fmaxf(ib[2], cx + fx * (xb >= 0.f ? xb / zl : xb / zh) + 1.5f);
+        ib[1] = fminf(ib[1], cy + fy * (ya >= 0.f ? ya / zh : ya / zl) - 1.5f);
+        ib[3] = fmaxf(ib[3], cy + fy * (yb >= 0.f ? yb / zl : yb / zh) + 1.5f);
+      }
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+    for (int of = 16; of; of >>= 1) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], of));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], of));
+    }
+  for (int of = 16; of; of >>= 1) {
+    ib[0] = fminf(ib[0], __shfl_xor_sync(0xffffffffu, ib[0], of));
+    ib[1] = fminf(ib[1], __shfl_xor_sync(0xffffffffu, ib[1], of));
+    ib[2] = fmaxf(ib[2], __shfl_xor_sync(0xffffffffu, ib[2], of));
+    ib[3] = fmaxf(ib[3], __shfl_xor_sync(0xffffffffu, ib[3], of));
+  }
+  if (lane < 3) {
+    o.lo[lane] = lo[lane] - radius - 1e-3f;
+    o.hi[lane] = hi[lane] + radius + 1e-3f;
+  }
+  if (lane < 4) o.img_box[lane] = ib[lane];
+}
 
 // one thread = PIX consecutive decimated pixels of one state
 template <int PIX>
@@ -215,114 +261,130 @@ k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __rest
 #define TGT_W 32
 #define TGT_H 16
 
-__global__ void __launch_bounds__(TGF_BLOCK)
+#define TGT_PER_WARP 5  // tiles per warp: the depth of tile i + 1 is in flight while tile i is processed
+
+__device__ __forceinline__ void tgt_load(const float* __restrict__ img, int H, int W, int tile, int tiles_x, int ntiles, int lane,
+                                         float4 (&d)[4]) {
+  const int ty0 = tile / tiles_x, tx0 = tile - ty0 * tiles_x;
+  const int u = tx0 * TGT_W + 4 * (lane & 7), vb = ty0 * TGT_H + (lane >> 3);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int v = vb + 4 * j;
+    d[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (tile < ntiles && v < H && u < W) d[j] = __ldcs(reinterpret_cast<const float4*>(img + (size_t)v * W + u));
+  }
+}
+
+__global__ void __launch_bounds__(TGF_BLOCK, 3)
 k_self_filter_tiles(const float* __restrict__ depth, const TgFilterState* __restrict__ prep, TgDepthParams p, float radius,
                     uint8_t* __restrict__ mask) {
   __shared__ TgFilterState st;
   const int s = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tiles_x = (p.W + TGT_W - 1) / TGT_W, tiles_y = (p.H + TGT_H - 1) / TGT_H, ntiles = tiles_x * tiles_y;
+  const int tile0 = blockIdx.x * (TGF_BLOCK / 32) * TGT_PER_WARP + warp;  // this warp: tile0, tile0 + 8, ...
+  const float* img = depth + (size_t)s * p.H * p.W;
+  uint8_t* mrow = mask + (size_t)s * p.H * p.W;
+  float4 dn[4];
+  tgt_load(img, p.H, p.W, tile0, tiles_x, ntiles, lane, dn);  // first tile's depth is in flight during the state load
   {
     const float* src = reinterpret_cast<const float*>(prep + s);
     float* dst = reinterpret_cast<float*>(&st);
-    for (int j = threadIdx.x; j < (int)(sizeof(TgFilterState) / 4); j += TGF_BLOCK) dst[j] = src[j];
+    for (int j = threadIdx.x; j < (int)(sizeof(TgFilterState) / 4); j += TGF_BLOCK) dst[j] = __ldg(src + j);
   }
   __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int tiles_x = (p.W + TGT_W - 1) / TGT_W, tiles_y = (p.H + TGT_H - 1) / TGT_H;
-  const int tile = blockIdx.x * (TGF_BLOCK / 32) + warp;
-  if (tile >= tiles_x * tiles_y) return;
-  const int ty0 = tile / tiles_x, tx0 = tile - ty0 * tiles_x;
-  const int u0 = tx0 * TGT_W, v0 = ty0 * TGT_H;
-  // candidate spheres of the tile
   const float rp = radius + 2e-3f;
   const float ifx = (float)(1.0 / p.fx), ify = (float)(1.0 / p.fy), cxf = (float)p.cx, cyf = (float)p.cy;
-  const float a0 = ((float)u0 - 0.5f - cxf) * ifx, a1 = ((float)(u0 + TGT_W) - 0.5f - cxf) * ifx;
-  const float b0 = ((float)v0 - 0.5f - cyf) * ify, b1 = ((float)(v0 + TGT_H) - 0.5f - cyf) * ify;
-  uint32_t m[4];
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const int j = lane + 32 * q;
-    bool c = false;
-    if (j < TGM_N_SPHERES) {
-      const float X = st.cc[3 * j], Y = st.cc[3 * j + 1], Z = st.cc[3 * j + 2];
-      const float zl = fmaxf(fmaxf(Z - rp, p.zmin - 1e-3f), 0.f), zh = fminf(Z + rp, p.zmax + 1e-3f);
-      if (zl <= zh) {
-        const float xmin = (a0 >= 0.f ? zl : zh) * a0, xmax = (a1 >= 0.f ? zh : zl) * a1;
-        const float ymin = (b0 >= 0.f ? zl : zh) * b0, ymax = (b1 >= 0.f ? zh : zl) * b1;
-        c = xmin <= X + rp && xmax >= X - rp && ymin <= Y + rp && ymax >= Y - rp;
-      }
-    }
-    m[q] = __ballot_sync(0xffffffffu, c);
-  }
-  // depth of this lane's 16 pixels
   const int tx = lane & 7, tyy = lane >> 3;
-  const int u = u0 + 4 * tx;
-  const float* img = depth + (size_t)s * p.H * p.W;
-  float z[16];
+  for (int it = 0; it < TGT_PER_WARP; ++it) {
+    const int tile = tile0 + it * (TGF_BLOCK / 32);
+    if (tile >= ntiles) break;  // warp-uniform
+    float z[16];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const int v = v0 + tyy + 4 * j;
-    float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (v < p.H && u < p.W) d = __ldg(reinterpret_cast<const float4*>(img + (size_t)v * p.W + u));
-    z[4 * j] = d.x; z[4 * j + 1] = d.y; z[4 * j + 2] = d.z; z[4 * j + 3] = d.w;
-  }
-  uint32_t ok = 0;
+    for (int j = 0; j < 4; ++j) {
+      z[4 * j] = dn[j].x; z[4 * j + 1] = dn[j].y; z[4 * j + 2] = dn[j].z; z[4 * j + 3] = dn[j].w;
+    }
+    if (it + 1 < TGT_PER_WARP) tgt_load(img, p.H, p.W, tile + TGF_BLOCK / 32, tiles_x, ntiles, lane, dn);
+    const int ty0 = tile / tiles_x, tx0 = tile - ty0 * tiles_x;
+    const int u0 = tx0 * TGT_W, v0 = ty0 * TGT_H, u = u0 + 4 * tx;
+    // candidate spheres of the tile (skipped when the tile misses the robot's image-space box)
+    uint32_t m[4] = {0u, 0u, 0u, 0u};
+    if ((float)(u0 + TGT_W) >= st.img_box[0] && (float)u0 <= st.img_box[2] && (float)(v0 + TGT_H) >= st.img_box[1] &&
+        (float)v0 <= st.img_box[3]) {
+      const float a0 = ((float)u0 - 0.5f - cxf) * ifx, a1 = ((float)(u0 + TGT_W) - 0.5f - cxf) * ifx;
+      const float b0 = ((float)v0 - 0.5f - cyf) * ify, b1 = ((float)(v0 + TGT_H) - 0.5f - cyf) * ify;
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    float zz = z[k];
-    if (isnan(zz)) zz = 0.f;  // np.nan_to_num; +-inf become +-FLT_MAX, which the range test rejects like the reference
-    else if (isinf(zz)) zz = zz > 0 ? 3.4028234663852886e38f : -3.4028234663852886e38f;
-    z[k] = zz;
-    if (zz > 0.f && zz >= p.zmin && zz <= p.zmax) ok |= 1u << k;
-  }
-  if ((m[0] | m[1] | m[2] | m[3]) != 0u) {  // warp-uniform: the robot may be visible in this tile
-    uint32_t cand = 0;  // pixels whose depth lies in some candidate sphere's depth interval
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      uint32_t bits = m[q];
-      while (bits) {
-        const int j = 32 * q + __ffs(bits) - 1;
-        bits &= bits - 1;
-        const float Z = st.cc[3 * j + 2];
-#pragma unroll
-        for (int k = 0; k < 16; ++k) cand |= (fabsf(z[k] - Z) < rp ? 1u : 0u) << k;
+      for (int q = 0; q < 4; ++q) {
+        const int j = lane + 32 * q;
+        bool c = false;
+        if (j < TGM_N_SPHERES) {
+          const float X = st.cc[3 * j], Y = st.cc[3 * j + 1], Z = st.cc[3 * j + 2];
+          const float zl = fmaxf(fmaxf(Z - rp, p.zmin - 1e-3f), 0.f), zh = fminf(Z + rp, p.zmax + 1e-3f);
+          if (zl <= zh) {
+            const float xmin = (a0 >= 0.f ? zl : zh) * a0, xmax = (a1 >= 0.f ? zh : zl) * a1;
+            const float ymin = (b0 >= 0.f ? zl : zh) * b0, ymax = (b1 >= 0.f ? zh : zl) * b1;
+            c = xmin <= X + rp && xmax >= X - rp && ymin <= Y + rp && ymax >= Y - rp;
+          }
+        }
+        m[q] = __ballot_sync(0xffffffffu, c);
       }
     }
-    cand &= ok;
-    while (cand) {  // rare: exact transform + exact test, same arithmetic as the generic kernel
-      const int k = __ffs(cand) - 1;
-      cand &= cand - 1;
-      const int uu = u + (k & 3), vv = v0 + tyy + 4 * (k >> 2);
-      float zz = 0.f;
+    // validity: NaN fails every compare and -inf fails z > 0 exactly like np.nan_to_num's 0 / -FLT_MAX;
+    // +inf behaves like +FLT_MAX against any zmax
+    uint32_t ok = 0;
 #pragma unroll
-      for (int kk = 0; kk < 16; ++kk)
-        if (kk == k) zz = z[kk];  // register select: keeps z[] out of local memory
-      const float xc = (float)((((double)(float)uu - p.cx) * (double)zz) / p.fx);
-      const float yc = (float)((((double)(float)vv - p.cy) * (double)zz) / p.fy);
-      const float wx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[0]), __fmul_rn(yc, st.cam_r[1])), __fmul_rn(zz, st.cam_r[2])), st.cam_t[0]);
-      const float wy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[3]), __fmul_rn(yc, st.cam_r[4])), __fmul_rn(zz, st.cam_r[5])), st.cam_t[1]);
-      const float wz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[6]), __fmul_rn(yc, st.cam_r[7])), __fmul_rn(zz, st.cam_r[8])), st.cam_t[2]);
-      bool inside = false;
+    for (int k = 0; k < 16; ++k)
+      if (z[k] > 0.f && z[k] >= p.zmin && z[k] <= p.zmax) ok |= 1u << k;
+    if ((m[0] | m[1] | m[2] | m[3]) != 0u) {  // warp-uniform: the robot may be visible in this tile
+      uint32_t cand = 0;  // pixels whose depth lies in some candidate sphere's depth interval
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         uint32_t bits = m[q];
         while (bits) {
           const int j = 32 * q + __ffs(bits) - 1;
           bits &= bits - 1;
-          const float dx = __fsub_rn(wx, st.c[3 * j]), dy = __fsub_rn(wy, st.c[3 * j + 1]), dz = __fsub_rn(wz, st.c[3 * j + 2]);
-          const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-          inside |= d2 < p.r2;
+          const float Z = st.cc[3 * j + 2];
+#pragma unroll
+          for (int k = 0; k < 16; ++k) cand |= (fabsf(z[k] - Z) < rp ? 1u : 0u) << k;
         }
       }
-      if (inside) ok &= ~(1u << k);
-    }
-  }
-  uint8_t* mrow = mask + (size_t)s * p.H * p.W;
+      cand &= ok;
+      while (cand) {  // rare: exact transform + exact test, same arithmetic as the generic kernel
+        const int k = __ffs(cand) - 1;
+        cand &= cand - 1;
+        const int uu = u + (k & 3), vv = v0 + tyy + 4 * (k >> 2);
+        float zz = 0.f;
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const int v = v0 + tyy + 4 * j;
-    if (v < p.H && u < p.W) {
-      const uint32_t b = (ok >> (4 * j)) & 0xFu;
-      *reinterpret_cast<uint32_t*>(mrow + (size_t)v * p.W + u) = (b & 1u) | ((b & 2u) << 7) | ((b & 4u) << 14) | ((b & 8u) << 21);
+        for (int kk = 0; kk < 16; ++kk)
+          if (kk == k) zz = z[kk];  // register select: keeps z[] out of local memory
+        if (isinf(zz)) zz = 3.4028234663852886e38f;  // np.nan_to_num (only reachable with zmax = inf)
+        const float xc = (float)((((double)(float)uu - p.cx) * (double)zz) / p.fx);
+        const float yc = (float)((((double)(float)vv - p.cy) * (double)zz) / p.fy);
+        const float wx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[0]), __fmul_rn(yc, st.cam_r[1])), __fmul_rn(zz, st.cam_r[2])), st.cam_t[0]);
+        const float wy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[3]), __fmul_rn(yc, st.cam_r[4])), __fmul_rn(zz, st.cam_r[5])), st.cam_t[1]);
+        const float wz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[6]), __fmul_rn(yc, st.cam_r[7])), __fmul_rn(zz, st.cam_r[8])), st.cam_t[2]);
+        bool inside = false;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint32_t bits = m[q];
+          while (bits) {
+            const int j = 32 * q + __ffs(bits) - 1;
+            bits &= bits - 1;
+            const float dx = __fsub_rn(wx, st.c[3 * j]), dy = __fsub_rn(wy, st.c[3 * j + 1]), dz = __fsub_rn(wz, st.c[3 * j + 2]);
+            const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            inside |= d2 < p.r2;
+          }
+        }
+        if (inside) ok &= ~(1u << k);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int v = v0 + tyy + 4 * j;
+      if (v < p.H && u < p.W) {
+        const uint32_t b = (ok >> (4 * j)) & 0xFu;
+        __stcs(reinterpret_cast<uint32_t*>(mrow + (size_t)v * p.W + u), (b & 1u) | ((b & 2u) << 7) | ((b & 4u) << 14) | ((b & 8u) << 21));
+      }
     }
   }
 }
@@ -345,11 +407,11 @@ extern "C" int tg_self_filter_depth(const float* depth, int H, int W, int stride
   p.r2 = (float)((double)radius * (double)radius);
   TgFilterState* prep = nullptr;
   TG_CUDA(cudaMallocAsync(&prep, sizeof(TgFilterState) * (size_t)S, st));
-  k_filter_prepare<<<tg_div_up(S, 128), 128, 0, st>>>(states, (int)S, radius, prep);
+  k_filter_prepare<<<tg_div_up(S, 4), 128, 0, st>>>(states, (int)S, radius, p, prep);
   const int npx = p.Hs * p.Ws;
   if (stride == 1 && world == nullptr && (W & 3) == 0 && ((uintptr_t)mask & 3) == 0) {
     const int tiles = tg_div_up(W, TGT_W) * tg_div_up(H, TGT_H);
-    dim3 grid(tg_div_up(tiles, TGF_BLOCK / 32), (unsigned)S);
+    dim3 grid(tg_div_up(tiles, (TGF_BLOCK / 32) * TGT_PER_WARP), (unsigned)S);
     k_self_filter_tiles<<<grid, TGF_BLOCK, 0, st>>>(depth, prep, p, radius, mask);
   } else {
     dim3 grid(tg_div_up(npx, TGF_BLOCK * 4), (unsigned)S);

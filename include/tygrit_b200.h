@@ -163,6 +163,35 @@ int tg_self_filter_depth(const float* depth, int H, int W, int stride, const dou
                          const float* states, int64_t S, float radius, float zmin, float zmax,
                          uint8_t* mask, float* world, void* stream);
 
+/* ---- device-resident ingest and belief merge (belief_state/pointcloud_scene.py:92-268) ------ */
+/* Order-preserving compaction: out receives the points whose flag byte is non-zero, in input
+ * order (numpy boolean-mask order); *count (DEVICE int) the number kept (may exceed capacity:
+ * only the first `capacity` are written).  All pointers DEVICE.                              */
+int tg_compact_points(const float* points, const uint8_t* flags, int64_t N, float* out,
+                      int64_t capacity, int* count, void* stream);
+/* First point of every voxel over vstack(base, add), voxel key floor(p / voxel) evaluated in f32
+ * (utils/pointcloud.py:13-64).  keep_add[j] = 1 iff add[j] is the first point of a voxel no base
+ * point falls in.  voxel_downsample(points) is the nb = 0 case; merge_dedup(base, add) keeps all
+ * of base plus the flagged add points.  Points with |coordinate / voxel| >= 2^20 or non-finite
+ * are never merged (kept) and counted in *unpackable (DEVICE int or NULL).                     */
+int tg_voxel_first(const float* base, int64_t nb, const float* add, int64_t na, float voxel,
+                   uint8_t* keep_add, int* unpackable, void* stream);
+/* One depth frame -> filtered world cloud, fused: back-projection (utils/depth.py:13-84, stride-
+ * decimated, K HOST 3x3 f64, T_wc HOST 4x4 f64 camera-to-world), z range, XY crop around the camera
+ * position (crop_radius < 0: off), ground filter z > ground_z (NaN: off), robot self-filter against
+ * `centres` (DEVICE n x 3 f32, strict d2 < r2 removes; n = 0: off).  out_points DEVICE capacity x 3
+ * in row-major pixel order, *count DEVICE int.                                                   */
+int tg_ingest_depth(const float* depth, int H, int W, int stride, const double* K, const double* T_wc,
+                    float zmin, float zmax, float crop_radius, float ground_z, const float* centres,
+                    int n_centres, float robot_radius, float* out_points, int64_t capacity, int* count,
+                    void* stream);
+/* Carve flags for the accumulated map: mode 0 = points_in_frustum_mask (utils/pointcloud.py:93-133),
+ * mode 1 = free-space ray test against `depth` (height x width DEVICE f32,
+ * pointcloud_scene.py:218-262).  keep[i] = 0 for the points the reference removes.               */
+int tg_carve_flags(const float* points, int64_t N, int mode, const double* K, const double* T_wc,
+                   float zmin, float zmax, int width, int height, const float* depth,
+                   float merge_radius, uint8_t* keep, void* stream);
+
 /* ---- synthetic input (benchmark support, not part of the reference surface) ----- */
 /* Analytic head-camera depth frames: rays against the 8 x 6 x 2.6 m room shell, `nb`
  * furniture boxes (DEVICE nb x 6: lo xyz, hi xyz; nb <= 64) and the robot's own 111

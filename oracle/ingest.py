@@ -138,5 +138,48 @@ def merge_add_index(base, add, radius):
     return ai
 
 
+def _to_camera_f32(points, T_wc):
+    """``(points - t) @ rot`` in f32, explicit x, y, z summation order (BLAS order is unspecified; <= 1 ulp)."""
+    T = np.asarray(T_wc, dtype=np.float64)
+    rot = T[:3, :3].astype(np.float32)
+    t = T[:3, 3].astype(np.float32)
+    d = np.asarray(points, dtype=np.float32) - t
+    return (d[:, 0:1] * rot[None, 0, :] + d[:, 1:2] * rot[None, 1, :]) + d[:, 2:3] * rot[None, 2, :]
+
+
+def frustum_mask(points, K, T_wc, z_range, width=640, height=480):
+    """``points_in_frustum_mask`` (utils/pointcloud.py:93-133): True = inside the camera frustum."""
+    K = np.asarray(K, dtype=np.float64)
+    pc = _to_camera_f32(points, T_wc)
+    z = pc[:, 2]
+    mz = (z >= np.float32(z_range[0])) & (z <= np.float32(z_range[1]))
+    zs = np.where(mz, z, np.float32(1.0)).astype(np.float64)
+    u = pc[:, 0].astype(np.float64) * K[0, 0] / zs + K[0, 2]
+    v = pc[:, 1].astype(np.float64) * K[1, 1] / zs + K[1, 2]
+    return mz & (u >= 0) & (u < width) & (v >= 0) & (v < height)
+
+
+def raycast_keep(points, depth, K, T_wc, merge_radius):
+    """Free-space carve of ``_update_ray_casting`` (pointcloud_scene.py:218-262): False = removed."""
+    K = np.asarray(K, dtype=np.float64)
+    depth = np.asarray(depth, dtype=np.float32)
+    pc = _to_camera_f32(points, T_wc)
+    zc = pc[:, 2]
+    valid = zc > 1e-3
+    zs = np.where(valid, zc, np.float32(1.0)).astype(np.float64)
+    u = pc[:, 0].astype(np.float64) * K[0, 0] / zs + K[0, 2]
+    v = pc[:, 1].astype(np.float64) * K[1, 1] / zs + K[1, 2]
+    ui, vi = np.rint(u).astype(np.int64), np.rint(v).astype(np.int64)
+    h, w = depth.shape
+    check = valid & (ui >= 0) & (ui < w) & (vi >= 0) & (vi < h)
+    keep = np.ones(len(pc), dtype=bool)
+    idx = np.where(check)[0]
+    zm = depth[vi[idx], ui[idx]]
+    with np.errstate(invalid="ignore"):
+        free = (zm > 0) & np.isfinite(zm) & (zc[idx] < (zm - np.float32(merge_radius)))
+    keep[idx[free]] = False
+    return keep
+
+
 __all__ = [n for n in dir() if not n.startswith("_")]
 _ = fm  # model import kept for callers that want radii

@@ -2,7 +2,8 @@
 
 The package holds only what the hot path needs: the CUDA kernels + C ABI (``csrc/``, built into
 ``lib/libtygrit_b200.so``) and the host-side mirror of the reference interface
-(``planner.B200Planner``, ``robot_filter.filter_robot_points``, ``fk.B200BatchFK``).
+(``planner.B200Planner``, ``robot_filter.filter_robot_points``, ``fk.B200BatchFK``,
+``scene.B200Scene`` + ``ingest`` for the device-resident cloud ingest and belief merge).
 Importing the package does not load CUDA; the first call into the engine does, and fails loudly
 if the library is missing (there is no CPU fallback).
 """
@@ -38,4 +39,8 @@ def __getattr__(name):  # lazy: torch / CUDA only when the engine is touched
         from . import fk
 
         return getattr(fk, name)
+    if name in ("B200Scene", "PointCloudSceneConfig", "SceneConfig"):
+        from . import scene
+
+        return getattr(scene, name)
     raise AttributeError(name)

@@ -59,6 +59,18 @@ _SIGS = {
         [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_float,
          C.c_void_p, C.c_void_p, C.c_void_p],
     ),
+    "tg_compact_points": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "tg_voxel_first": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "tg_ingest_depth": (
+        C.c_int,
+        [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float,
+         C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p],
+    ),
+    "tg_carve_flags": (
+        C.c_int,
+        [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p,
+         C.c_float, C.c_void_p, C.c_void_p],
+    ),
     "tg_synth_depth": (
         C.c_int,
         [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float, C.c_uint64, C.c_void_p,

@@ -78,6 +78,12 @@ class B200Planner:
     def update_environment(self, points, base_pose) -> None:
         """Sync collision world: set base pose and replace the point cloud (vamp_preview.py:183-192)."""
         self.set_base_params(base_pose)
+        if hasattr(points, "is_cuda") and points.is_cuda:   # device-resident cloud: no host round trip
+            if points.numel() > 0:
+                self.add_pointcloud(points)
+            else:
+                self.clear_pointclouds()
+            return
         pts = np.asarray(points)
         if pts.size > 0:
             self.add_pointcloud(pts)
@@ -159,9 +165,17 @@ class B200Planner:
         self._world.set_point_radius(float(radius))
         is_cuda = hasattr(points, "is_cuda") and points.is_cuda
         self._world.build(points if is_cuda else np.asarray(points, dtype=np.float32))
-        pts = points.detach().cpu().numpy() if is_cuda else np.asarray(points)
+        pad = self._config.bounds_padding
+        if is_cuda:  # device cloud (B200Scene.get_pointcloud_device): only the four XY bounds come back
+            if points.numel() > 0 and points.ndim == 2 and points.shape[1] >= 2:
+                lo, hi = points[:, :2].amin(dim=0), points[:, :2].amax(dim=0)
+                import torch
+
+                b = torch.cat((lo, hi)).tolist()
+                self._pc_bounds_xy = (b[0] - pad, b[2] + pad, b[1] - pad, b[3] + pad)
+            return
+        pts = np.asarray(points)
         if pts.size > 0 and pts.ndim == 2 and pts.shape[1] >= 2:
-            pad = self._config.bounds_padding
             mn, mx = pts[:, :2].min(axis=0), pts[:, :2].max(axis=0)
             self._pc_bounds_xy = (float(mn[0] - pad), float(mx[0] + pad), float(mn[1] - pad), float(mx[1] + pad))
 

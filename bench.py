@@ -57,6 +57,19 @@ def peaks():
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "source": "fallback"}
 
 
+def traffic_from_profile(cfg_per_launch, vpm):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one k_check_configs launch from the committed
+    `ncu --set full` capture (profiles/traffic.json); None when the capture was taken at another launch shape."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(path):
+        return None
+    t = json.load(open(path)).get("k_check_configs")
+    if not t or int(t["configs_per_launch"]) != int(cfg_per_launch) or float(t.get("voxels_per_metre", vpm)) != float(vpm):
+        return None
+    return {"bytes_per_launch": t["dram_bytes_read"] + t["dram_bytes_write"], "algorithmic_bytes_per_launch": B_CFG * cfg_per_launch,
+            "source": t["source"]}
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons through NVML while the timed region runs."""
 
@@ -280,7 +293,7 @@ def main():
         "algorithmic_flop_per_config": F_CFG, "configs_per_launch": cfg_per_launch, "avg_launch_ms": k1_ms,
         "share_of_step": tim["phase1_ms"] / elapsed_ms if world == 1 else None,
         "phase2_share_of_step": tim["phase2_ms"] / elapsed_ms if world == 1 else None,
-        "traffic": None,
+        "traffic": traffic_from_profile(cfg_per_launch, args.vpm),
         "hbm": {"achieved": cfg_per_launch * B_CFG / (k1_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": cfg_per_launch * B_CFG / (k1_ms * 1e-3) / 1e9 / pk["hbm_gbs"], "algorithmic_bytes_per_config": B_CFG,
                 "peak_source": pk["source"]},

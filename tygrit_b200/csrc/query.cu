@@ -179,7 +179,7 @@ __device__ __forceinline__ void tg_emit_frame(const TgFrame& F, const TgBase& b,
     const float3 pb = tg_frame_apply(F, l.x, l.y, l.z);
     const float3 pw = tg_to_world(b, pb.x, pb.y, pb.z);
     s_sph[slot] = make_float4(pw.x, pw.y, pw.z, l.w + r_pt);
-    s_own[slot] = (uint16_t)threadIdx.x;
+    s_own[slot] = (uint16_t)(threadIdx.x >> 1);  // item index inside the batch
   }
 }
 
@@ -196,6 +196,8 @@ __global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueu
   __shared__ float4 s_sph[TGR_CAP];
   __shared__ uint16_t s_own[TGR_CAP];
   __shared__ uint32_t s_key[TGR_CAP];
+  __shared__ uint16_t s_rest[TGR_CAP];
+  __shared__ unsigned s_nrest;
   __shared__ uint32_t s_best[TGR_ITEMS];
   __shared__ uint32_t s_target[TGR_ITEMS];
   __shared__ uint8_t s_done[TGR_ITEMS];
@@ -210,22 +212,27 @@ __global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueu
     __syncthreads();
     const unsigned batch = s_batch;
     if (batch >= nbatch) break;
-    const unsigned i = batch * TGR_ITEMS + threadIdx.x;
+    // two threads per item: part 0 lists the base / torso / head spheres (kernel order 0..54, base yaw and
+    // torso lift only), part 1 runs the arm chain (55..110)
+    const unsigned itx = threadIdx.x >> 1, part = threadIdx.x & 1u;
+    const unsigned i = batch * TGR_ITEMS + itx;
     TgItem it;
     int cnt = 0;
-    if (threadIdx.x < TGR_ITEMS) {
-      if (i < n) {
-        const float4* src = reinterpret_cast<const float4*>(qu.items + i);
-        float4* dst = reinterpret_cast<float4*>(&it);
+    if (i < n) {
+      const float4* src = reinterpret_cast<const float4*>(qu.items + i);
+      float4* dst = reinterpret_cast<float4*>(&it);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) dst[k] = src[k];
-        s_target[threadIdx.x] = it.target;
-        const bool dead = valid[it.target] == 0;  // edge already refuted by another sample
-        s_done[threadIdx.x] = dead ? 1 : 0;
-        if (!dead) cnt = __popc(it.mask[0]) + __popc(it.mask[1]) + __popc(it.mask[2]) + __popc(it.mask[3]);
-      } else {
-        s_done[threadIdx.x] = 1;
+      for (int k = 0; k < 4; ++k) dst[k] = src[k];
+      const bool dead = valid[it.target] == 0;  // edge already refuted by another sample
+      if (part == 0) {
+        s_target[itx] = it.target;
+        s_done[itx] = dead ? 1 : 0;
       }
+      if (!dead)
+        cnt = part == 0 ? __popc(it.mask[0]) + __popc(it.mask[1] & 0x007FFFFFu)
+                        : __popc(it.mask[1] >> 23) + __popc(it.mask[2]) + __popc(it.mask[3]);
+    } else if (part == 0) {
+      s_done[itx] = 1;
     }
     // block exclusive prefix sum of cnt
     int incl = cnt;
@@ -249,12 +256,15 @@ __global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueu
         int ord = off;
         TgFrame T, F, H;
         tg_frame_identity(T);
-        tg_emit_frame(T, b, g.r_pt, tg_mask_range(it.mask, 0, 20), 0, ord, w0, s_sph, s_own);
-        T.t[0] = TGM_OFF_TORSO_X;
-        T.t[2] = TGM_OFF_TORSO_Z + cfg[3];
-        tg_emit_frame(T, b, g.r_pt, tg_mask_range(it.mask, 20, 52), 20, ord, w0, s_sph, s_own);
-        tg_emit_frame(T, b, g.r_pt, tg_mask_range(it.mask, 52, 55), 52, ord, w0, s_sph, s_own);
-        if ((it.mask[1] >> 23) | it.mask[2] | it.mask[3]) {  // any arm sphere (k >= 55)
+        if (part == 0) {
+          tg_emit_frame(T, b, g.r_pt, tg_mask_range(it.mask, 0, 20), 0, ord, w0, s_sph, s_own);
+          T.t[0] = TGM_OFF_TORSO_X;
+          T.t[2] = TGM_OFF_TORSO_Z + cfg[3];
+          tg_emit_frame(T, b, g.r_pt, tg_mask_range(it.mask, 20, 52), 20, ord, w0, s_sph, s_own);
+          tg_emit_frame(T, b, g.r_pt, tg_mask_range(it.mask, 52, 55), 52, ord, w0, s_sph, s_own);
+        } else {
+          T.t[0] = TGM_OFF_TORSO_X;
+          T.t[2] = TGM_OFF_TORSO_Z + cfg[3];
           tg_frame_child(T, TGM_OFF_SHOULDER_PAN_X, TGM_OFF_SHOULDER_PAN_Y, TGM_OFF_SHOULDER_PAN_Z, 4, cfg[4], F);
           tg_emit_frame(F, b, g.r_pt, tg_mask_range(it.mask, 55, 59), 55, ord, w0, s_sph, s_own);
           tg_frame_child(F, TGM_OFF_SHOULDER_LIFT_X, TGM_OFF_SHOULDER_LIFT_Y, TGM_OFF_SHOULDER_LIFT_Z, 3, cfg[5], H);
@@ -338,10 +348,17 @@ __global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueu
         }
         if (!__syncthreads_or(any)) break;
       }
-      // Step 3b: the remaining spheres of the items that are still open
-      for (int j = (int)warp; j < nw; j += TGR_BLOCK / 32) {
+      // Step 3b: the remaining spheres of the items that are still open, gathered into a dense list first
+      if (threadIdx.x == 0) s_nrest = 0;
+      __syncthreads();
+      for (int j = threadIdx.x; j < nw; j += TGR_BLOCK)
+        if (s_key[j] != 0xFFFFFFFFu && !s_done[s_own[j]]) s_rest[atomicAdd(&s_nrest, 1u)] = (uint16_t)j;
+      __syncthreads();
+      const int nrest = (int)s_nrest;
+      for (int r = (int)warp; r < nrest; r += TGR_BLOCK / 32) {
+        const int j = s_rest[r];
         const int own = s_own[j];
-        if (s_key[j] == 0xFFFFFFFFu || s_done[own]) continue;  // warp-uniform
+        if (s_done[own]) continue;  // warp-uniform
         const float4 c = s_sph[j];
         if (tg_warp_sphere_hits(g, c.x, c.y, c.z, c.w)) {
           TG_STAT(8, 1);

@@ -15,12 +15,17 @@
 #include "common.cuh"
 #include "fk.cuh"
 
+// Distance code of the voxel containing (gx, gy, gz) (voxel units).  Adding the 2^23 bias rounds to the
+// nearest voxel in the mantissa; subtracting the bit pattern of 2^23 as an unsigned and taking the
+// unsigned minimum with n - 1 clamps both sides at once — one DPX add-min per axis — because values
+// below the grid wrap to huge unsigned numbers.  They land on the far boundary voxel instead of the near
+// one, which is equivalent: every boundary voxel is at least W voxels from the cloud (tg_plan_grids pads
+// the box by W + 3), so both read "free".
 __device__ __forceinline__ int tg_probe(const TgGrid& g, float gx, float gy, float gz) {
-  const float fx = fminf(fmaxf(gx + g.bias[0], TG_MAGIC), g.hi[0]);
-  const float fy = fminf(fmaxf(gy + g.bias[1], TG_MAGIC), g.hi[1]);
-  const float fz = fminf(fmaxf(gz + g.bias[2], TG_MAGIC), g.hi[2]);
-  const unsigned idx = __float_as_uint(fx) + (unsigned)g.nx * __float_as_uint(fy) + (unsigned)g.nxy * __float_as_uint(fz) - g.idx_bias;
-  return (int)__ldg(g.df + idx);
+  const unsigned ux = __viaddmin_u32(__float_as_uint(gx + g.bias[0]), 0u - TG_MAGIC_BITS, (unsigned)(g.nx - 1));
+  const unsigned uy = __viaddmin_u32(__float_as_uint(gy + g.bias[1]), 0u - TG_MAGIC_BITS, (unsigned)(g.ny - 1));
+  const unsigned uz = __viaddmin_u32(__float_as_uint(gz + g.bias[2]), 0u - TG_MAGIC_BITS, (unsigned)(g.nz - 1));
+  return (int)__ldg(g.df + (ux + (unsigned)g.nx * uy + (unsigned)g.nxy * uz));
 }
 
 struct TgClass {

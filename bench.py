@@ -42,7 +42,7 @@ def parse():
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--configs", type=int, default=64 * 1024 * 1024, help="configurations per GPU per step")
     p.add_argument("--cpu-sample", type=int, default=4_000_000, help="configurations per CPU-baseline sample")
-    p.add_argument("--vpm", type=float, default=50.0, help="distance-grid voxels per metre")
+    p.add_argument("--vpm", type=float, default=72.0, help="distance-grid voxels per metre (static cloud: the finer grid pays, sweep in profiles/)")
     p.add_argument("--cpm", type=float, default=0.0, help="narrow-phase cells per metre (0 = library default)")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu", action="store_true")

@@ -54,8 +54,10 @@ __device__ __forceinline__ void tg_push_item(const TgGrid& g, TgQueue qu, TgCoun
 // compacted through a shared-memory ring so that stage B (91 spheres + the arm chain) always runs
 // with full warps.  Two block barriers per tile of TGC_BLOCK configurations.
 // ------------------------------------------------------------------------------------------------
-#define TGC_BLOCK 256
-#define TGC_RING 512  // >= 2 * TGC_BLOCK, power of two
+#ifndef TGC_BLOCK
+#define TGC_BLOCK 512  // 2 blocks of 16 warps per SM: warps of a block run the same code region, which the instruction cache likes (A/B in profiles/)
+#endif
+#define TGC_RING (2 * TGC_BLOCK)  // >= 2 * TGC_BLOCK, power of two
 
 struct TgRing {
   float cfg[11][TGC_RING];
@@ -83,10 +85,11 @@ __device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& t
   tg_push_item(g, qu, ctr, need, idx, cl.amb, cfg, valid);
 }
 
-__global__ void __launch_bounds__(TGC_BLOCK, 4)
+__global__ void __launch_bounds__(TGC_BLOCK, 1024 / TGC_BLOCK)
 k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm,
                 const float* __restrict__ base, int B, uint8_t* __restrict__ valid, TgQueue qu, TgCounters* ctr) {
-  __shared__ TgRing ring;
+  extern __shared__ __align__(16) unsigned char tgc_smem[];
+  TgRing& ring = *reinterpret_cast<TgRing*>(tgc_smem);
   __shared__ unsigned s_tail;
   if (threadIdx.x == 0) s_tail = 0;
   __syncthreads();
@@ -516,7 +519,8 @@ __global__ void k_fill_u8(uint8_t* p, int n, uint8_t v) {
 // resident blocks per SM of the two persistent kernels (queried once per env)
 int tg_query_occupancy(tg_env* env) {
   int a = 0, b = 0;
-  TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_check_configs, TGC_BLOCK, 0));
+  TG_CUDA(cudaFuncSetAttribute(k_check_configs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TgRing)));
+  TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_check_configs, TGC_BLOCK, sizeof(TgRing)));
   TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_resolve, TGR_BLOCK, 0));
   env->occ_configs = a > 0 ? a : 1;
   env->occ_resolve = b > 0 ? b : 1;
@@ -556,7 +560,7 @@ int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int6
         TG_CUDA(cudaEventRecord(ev[0], st));
       }
       const int blocks1 = min(tg_div_up(nb, TGC_BLOCK), env->sm_count * env->occ_configs);
-      k_check_configs<<<blocks1, TGC_BLOCK, 0, st>>>(env->grid, env->thr, ex, arm + 8 * off, base + 3 * off, nb, valid + off, qu,
+      k_check_configs<<<blocks1, TGC_BLOCK, sizeof(TgRing), st>>>(env->grid, env->thr, ex, arm + 8 * off, base + 3 * off, nb, valid + off, qu,
                                                      env->counters_dev);
       if (env->timing) TG_CUDA(cudaEventRecord(ev[1], st));
       if (!env->grid.empty) {

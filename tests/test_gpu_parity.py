@@ -396,13 +396,14 @@ def test_self_filter_depth_batch_vs_oracle():
             assert np.array_equal(fast, mask)
 
 
-@pytest.mark.parametrize("shape", [(480, 640), (100, 164)])
+@pytest.mark.parametrize("shape", [(480, 640, 24), (100, 164, 24), (480, 640, 96), (37, 2048, 5)])
 def test_self_filter_fast_path_equals_generic_kernel(shape):
-    """Full-resolution frames (and a size with ragged tiles): k_self_filter_tiles vs k_self_filter_depth."""
-    H, W = shape
+    """Full-resolution frames (a size with ragged tiles and a short last chunk, enough states for the shared-memory
+    ring to wrap several times, and a wide image with 3 rows per chunk): k_self_filter_stream vs k_self_filter_depth."""
+    H, W, n_states = shape
     K = synth.HEAD_CAMERA_K.copy()
     K[:2] *= W / 640.0
-    states = synth.random_states(24, seed=21)
+    states = synth.random_states(n_states, seed=21)
     states[::2, 12] = 0.9                                             # half of the states look down at the arm
     st = _cuda(states)
     bx = _cuda(np.array([[*lo, *hi] for lo, hi in synth.room_boxes()], np.float32))

@@ -389,6 +389,235 @@ k_self_filter_tiles(const float* __restrict__ depth, const TgFilterState* __rest
   }
 }
 
+// ---- K4 v3: streaming fast path (full-resolution frames, mask only) --------------------------------
+// Persistent blocks, two per SM.  A block owns a contiguous range of "chunks" (R full image rows of one
+// state = one contiguous piece of the depth array) and pulls them through a 4-stage shared-memory ring
+// with 1-D bulk async copies (cp.async.bulk + mbarrier complete_tx, L2 evict-first): one thread keeps
+// up to 4 x 20 KB per block = 160 KB per SM in flight, independent of register pressure and occupancy,
+// which is what an HBM-bound stream needs (6.5 TB/s x ~1 us latency = 44 KB per SM at the very least).
+// While a chunk is in flight the warps cull the robot's spheres against the chunk's 32-pixel-wide
+// tiles exactly like k_self_filter_tiles (sphere depth interval x projected box, conservative); the
+// 128-bit candidate mask of each tile goes to shared memory.  Consumers read 4 pixels per thread from
+// the ring (conflict-free LDS.128); a pixel costs three compares unless its tile has candidates AND its
+// depth falls into a candidate's depth interval — then it is transformed and tested with the generic
+// kernel's arithmetic (same rounding, same verdict), so the mask stays byte-identical.
+#ifndef TGS_STAGES
+#define TGS_STAGES 4
+#endif
+#ifndef TGS_STAGE_BYTES
+#define TGS_STAGE_BYTES 24576
+#endif
+#ifndef TGS_MAX_ROWS
+#define TGS_MAX_ROWS 8
+#endif
+
+__device__ __forceinline__ uint32_t tg_smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void tg_mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tg_smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void tg_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tg_smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tg_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+                   tg_smem_addr(dst)),
+               "l"(src), "r"(bytes), "r"(tg_smem_addr(bar)), "l"(policy)
+               : "memory");
+}
+__device__ __forceinline__ bool tg_mbar_try(uint32_t bar_addr, uint32_t parity) {
+  uint32_t done;
+  asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+               : "=r"(done)
+               : "r"(bar_addr), "r"(parity)
+               : "memory");
+  return done != 0;
+}
+// spinning warps take issue slots from the warps that have work: back off between polls
+__device__ __forceinline__ void tg_mbar_wait(uint32_t bar_addr, uint32_t parity, unsigned backoff_ns) {
+  while (!tg_mbar_try(bar_addr, parity)) __nanosleep(backoff_ns);
+}
+
+#define TGS_CONSUMERS 8                         // consumer warps; warp TGS_CONSUMERS is the producer
+#define TGS_THREADS ((TGS_CONSUMERS + 1) * 32)
+#define TGS_STATE_BYTES ((int)((sizeof(TgFilterState) + 127) / 128 * 128))
+#define TGS_SLOT_BYTES (TGS_STAGE_BYTES + TGS_STATE_BYTES)  // one ring slot = the chunk's depth rows + its robot state
+static_assert(sizeof(TgFilterState) % 16 == 0, "bulk copies move multiples of 16 bytes");
+
+__global__ void __launch_bounds__(TGS_THREADS, 2)
+k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __restrict__ prep, TgDepthParams p, float radius,
+                     uint8_t* __restrict__ mask, int R, int cpf, int total_chunks) {
+  extern __shared__ __align__(128) unsigned char tgs_smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tgs_smem + (size_t)TGS_STAGES * TGS_SLOT_BYTES);  // full[], empty[]
+  const uint32_t full0 = tg_smem_addr(bars), empty0 = full0 + 8 * TGS_STAGES;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // chunk i of this block is chunk blockIdx.x + i * gridDim.x: at any time the grid reads one contiguous window of
+  // the depth array, and the frames in which the robot fills the view (far more work) are spread over all blocks
+  const int G = (int)gridDim.x;
+  const int n = (int)blockIdx.x < total_chunks ? (total_chunks - (int)blockIdx.x + G - 1) / G : 0;
+  const int dS = G / cpf, dK = G - dS * cpf;
+  int s = (int)blockIdx.x / cpf, kc = (int)blockIdx.x - s * cpf;  // state and chunk-in-frame of chunk i, kept incrementally
+  const int W = p.W, H = p.H, w4 = W >> 2, ntx = (W + 31) >> 5;
+  if (tid == 0) {
+#pragma unroll
+    for (int k = 0; k < TGS_STAGES; ++k) {
+      tg_mbar_init(bars + k, 1);
+      tg_mbar_init(bars + TGS_STAGES + k, TGS_CONSUMERS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == TGS_CONSUMERS) {  // ---- producer: one thread keeps TGS_STAGES slots in flight
+    if (lane != 0) return;
+    uint64_t stream_once, keep;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(stream_once));
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
+    for (int i = 0, slot = 0, round = 0; i < n; ++i) {
+      if (round > 0) tg_mbar_wait(empty0 + 8 * slot, (uint32_t)(round - 1) & 1u, 200);
+      const int row0 = kc * R, rows = min(R, H - row0);
+      const uint32_t bytes = (uint32_t)rows * (uint32_t)W * 4u;
+      unsigned char* dst = tgs_smem + (size_t)slot * TGS_SLOT_BYTES;
+      tg_mbar_expect_tx(bars + slot, bytes + (uint32_t)sizeof(TgFilterState));
+      tg_bulk_g2s(dst, depth + ((size_t)s * H + row0) * W, bytes, bars + slot, stream_once);
+      tg_bulk_g2s(dst + TGS_STAGE_BYTES, prep + s, (uint32_t)sizeof(TgFilterState), bars + slot, keep);
+      s += dS; kc += dK;
+      if (kc >= cpf) { kc -= cpf; ++s; }
+      if (++slot == TGS_STAGES) { slot = 0; ++round; }
+    }
+    return;
+  }
+  // ---- consumers
+  // a point can only be inside a sphere of radius r if its camera-frame distance to the centre is below
+  // r + 2 mm, and it surely is if that distance is below r - 2 mm: the camera-frame and the world-frame
+  // arithmetic differ by rounding only (< 2e-5 m for |p| < 10 m).  The shell between is settled exactly.
+  const float rp = radius + 2e-3f, rout2 = rp * rp;
+  const float rin = fmaxf(radius - 2e-3f, 0.f), rin2 = rin * rin;
+  const float ifx = (float)(1.0 / p.fx), ify = (float)(1.0 / p.fy), cxf = (float)p.cx, cyf = (float)p.cy;
+  // z > 0 && z >= zmin  <=>  z >= max(zmin, smallest positive float); NaN fails every compare and -inf fails z > 0
+  // exactly like np.nan_to_num's 0 / -FLT_MAX; +inf behaves like +FLT_MAX against any zmax
+  const float zlo_ok = p.zmin > 0.f ? p.zmin : 1.401298464e-45f, zhi_ok = p.zmax;
+  const int lc = lane & 7, lr = lane >> 3;
+  for (int i = 0, slot = 0, round = 0; i < n; ++i) {
+    const int row0 = kc * R, rows = min(R, H - row0), nty = (rows + 3) >> 2;
+    const unsigned char* base = tgs_smem + (size_t)slot * TGS_SLOT_BYTES;
+    const float4* buf = reinterpret_cast<const float4*>(base);
+    const TgFilterState& st = *reinterpret_cast<const TgFilterState*>(base + TGS_STAGE_BYTES);
+    uint32_t* mrow = reinterpret_cast<uint32_t*>(mask + ((size_t)s * H + row0) * W);
+    tg_mbar_wait(full0 + 8 * slot, (uint32_t)round & 1u, 40);
+    // tile columns that meet the robot's image-space box (float -> int conversion saturates, +-inf are fine)
+    int tx_lo = 0x7fffffff, tx_hi = -1;
+    if ((float)(row0 + rows) >= st.img_box[1] && (float)row0 <= st.img_box[3]) {
+      tx_lo = (int)fmaxf(ceilf((st.img_box[0] - 32.f) * 0.03125f), 0.f);
+      tx_hi = (int)fminf(floorf(st.img_box[2] * 0.03125f), (float)ntx);
+    }
+    int tx = warp, ty = 0;
+    while (tx >= ntx) { tx -= ntx; ++ty; }
+    while (ty < nty) {  // one warp = one tile of 32 x 4 pixels; lane = 4 consecutive pixels of row 4 ty + lr
+      const int c4 = 8 * tx + lc, rr = 4 * ty + lr;
+      const int f = rr * w4 + c4;  // float4 index in the chunk = uint32 index in the chunk's mask rows
+      const bool have = c4 < w4 && rr < rows;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (have) v = buf[f];
+      const float z[4] = {v.x, v.y, v.z, v.w};
+      uint32_t ok = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) ok |= (z[k] >= zlo_ok && z[k] <= zhi_ok ? 1u : 0u) << k;
+      if (tx >= tx_lo && tx <= tx_hi) {  // warp-uniform
+        float zlo = INFINITY, zhi = -INFINITY;  // depth range of the tile's valid pixels
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (ok >> k & 1u) { zlo = fminf(zlo, z[k]); zhi = fmaxf(zhi, z[k]); }
+#pragma unroll
+        for (int of = 16; of; of >>= 1) {
+          zlo = fminf(zlo, __shfl_xor_sync(0xffffffffu, zlo, of));
+          zhi = fmaxf(zhi, __shfl_xor_sync(0xffffffffu, zhi, of));
+        }
+        uint32_t m[4] = {0u, 0u, 0u, 0u};
+        if (zlo <= zhi) {
+          // candidate spheres: depth interval meets the tile's depth range and, over that depth range, the tile's
+          // back-projected box meets the sphere's box (conservative)
+          const int u0 = tx << 5, v0 = row0 + 4 * ty;
+          const float a0 = ((float)u0 - 0.5f - cxf) * ifx, a1 = ((float)(u0 + 32) - 0.5f - cxf) * ifx;
+          const float b0 = ((float)v0 - 0.5f - cyf) * ify, b1 = ((float)(v0 + 4) - 0.5f - cyf) * ify;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int j = lane + 32 * q;
+            bool c = false;
+            if (j < TGM_N_SPHERES) {
+              const float X = st.cc[3 * j], Y = st.cc[3 * j + 1], Z = st.cc[3 * j + 2];
+              const float zl = fmaxf(Z - rp, zlo), zh = fminf(Z + rp, zhi);
+              if (zl <= zh) {
+                const float xmin = (a0 >= 0.f ? zl : zh) * a0, xmax = (a1 >= 0.f ? zh : zl) * a1;
+                const float ymin = (b0 >= 0.f ? zl : zh) * b0, ymax = (b1 >= 0.f ? zh : zl) * b1;
+                c = xmin <= X + rp && xmax >= X - rp && ymin <= Y + rp && ymax >= Y - rp;
+              }
+            }
+            m[q] = __ballot_sync(0xffffffffu, c);
+          }
+        }
+        if ((m[0] | m[1] | m[2] | m[3]) != 0u) {  // warp-uniform: the robot may be visible in this tile
+          const float ay = ((float)(row0 + rr) - cyf) * ify;
+          float ax[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) ax[k] = ((float)(4 * c4 + k) - cxf) * ifx;
+          uint32_t inside = 0, shell = 0;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint32_t bits = m[q];
+            while (bits) {
+              const int j = 32 * q + __ffs(bits) - 1;
+              bits &= bits - 1;
+              const float X = st.cc[3 * j], Y = st.cc[3 * j + 1], Z = st.cc[3 * j + 2];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const float dx = fmaf(z[k], ax[k], -X), dy = fmaf(z[k], ay, -Y), dz = z[k] - Z;
+                const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                inside |= (d2 < rin2 ? 1u : 0u) << k;
+                shell |= (d2 < rout2 ? 1u : 0u) << k;
+              }
+            }
+          }
+          uint32_t need = shell & ~inside & ok;
+          ok &= ~inside;
+          while (need) {  // rare (2 mm shells): exact transform + exact test, same arithmetic as the generic kernel
+            const int k = __ffs(need) - 1;
+            need &= need - 1;
+            const int uu = 4 * c4 + k, vv = row0 + rr;
+            float zz = k == 0 ? z[0] : k == 1 ? z[1] : k == 2 ? z[2] : z[3];
+            if (isinf(zz)) zz = 3.4028234663852886e38f;  // np.nan_to_num (only reachable with zmax = inf)
+            const float xc = (float)((((double)(float)uu - p.cx) * (double)zz) / p.fx);
+            const float yc = (float)((((double)(float)vv - p.cy) * (double)zz) / p.fy);
+            const float wx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[0]), __fmul_rn(yc, st.cam_r[1])), __fmul_rn(zz, st.cam_r[2])), st.cam_t[0]);
+            const float wy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[3]), __fmul_rn(yc, st.cam_r[4])), __fmul_rn(zz, st.cam_r[5])), st.cam_t[1]);
+            const float wz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[6]), __fmul_rn(yc, st.cam_r[7])), __fmul_rn(zz, st.cam_r[8])), st.cam_t[2]);
+            bool in = false;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint32_t bits = m[q];
+              while (bits) {
+                const int j = 32 * q + __ffs(bits) - 1;
+                bits &= bits - 1;
+                const float dx = __fsub_rn(wx, st.c[3 * j]), dy = __fsub_rn(wy, st.c[3 * j + 1]), dz = __fsub_rn(wz, st.c[3 * j + 2]);
+                const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+                in |= d2 < p.r2;
+              }
+            }
+            if (in) ok &= ~(1u << k);
+          }
+        }
+      }
+      // 4 mask bytes from 4 bits: bit k of ok lands on bit 8k (k + 7k) of the product, no carries
+      if (have) __stcs(mrow + f, (ok * 0x00204081u) & 0x01010101u);
+      tx += TGS_CONSUMERS;
+      while (tx >= ntx) { tx -= ntx; ++ty; }
+    }
+    __syncwarp();
+    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty0 + 8 * slot) : "memory");
+    s += dS; kc += dK;
+    if (kc >= cpf) { kc -= cpf; ++s; }
+    if (++slot == TGS_STAGES) { slot = 0; ++round; }
+  }
+}
+
 extern "C" int tg_self_filter_depth(const float* depth, int H, int W, int stride, const double* K, const float* states, int64_t S,
                                     float radius, float zmin, float zmax, uint8_t* mask, float* world, void* stream_) {
   TG_CHECK_ARG(H > 0 && W > 0 && stride >= 1 && S >= 0 && S < 65536, "tg_self_filter_depth: bad shape (S < 65536)");
@@ -409,6 +638,25 @@ extern "C" int tg_self_filter_depth(const float* depth, int H, int W, int stride
   TG_CUDA(cudaMallocAsync(&prep, sizeof(TgFilterState) * (size_t)S, st));
   k_filter_prepare<<<tg_div_up(S, 4), 128, 0, st>>>(states, (int)S, radius, p, prep);
   const int npx = p.Hs * p.Ws;
+#ifndef TG_K4_TILES
+  if (stride == 1 && world == nullptr && (W & 3) == 0 && ((uintptr_t)mask & 3) == 0 && W * 4 <= TGS_STAGE_BYTES &&
+      (long long)S * H < (1ll << 28)) {
+    static bool attr_set[64] = {};
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const size_t smem = (size_t)TGS_STAGES * TGS_SLOT_BYTES + 2 * TGS_STAGES * sizeof(uint64_t);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      TG_CUDA(cudaFuncSetAttribute(k_self_filter_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_set[dev] = true;
+    }
+    const int R = min(TGS_MAX_ROWS, TGS_STAGE_BYTES / (W * 4));
+    const int cpf = tg_div_up(H, R);
+    const int total = cpf * (int)S;
+    const int blocks = min(sms * 2, total);
+    k_self_filter_stream<<<blocks, TGS_THREADS, smem, st>>>(depth, prep, p, radius, mask, R, cpf, total);
+  } else
+#endif
   if (stride == 1 && world == nullptr && (W & 3) == 0 && ((uintptr_t)mask & 3) == 0) {
     const int tiles = tg_div_up(W, TGT_W) * tg_div_up(H, TGT_H);
     dim3 grid(tg_div_up(tiles, (TGF_BLOCK / 32) * TGT_PER_WARP), (unsigned)S);

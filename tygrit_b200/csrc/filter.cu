@@ -249,146 +249,6 @@ k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __rest
   }
 }
 
-// ---- fast path: full-resolution frames, mask only ---------------------------------------------
-// One warp = one 32 x 16 pixel tile (lane = 4 consecutive pixels x 4 rows, 128-bit depth loads, 32-bit
-// mask stores).  The warp first finds the spheres that can touch the tile at all: a sphere at camera-
-// frame (X, Y, Z) can only contain back-projected points with depth in [Z - r, Z + r] whose image
-// position lies in its projected box (conservative, 2 mm margin; 4 spheres per lane + ballot).  For
-// almost every tile that set is empty and a pixel costs one load, three compares and a quarter of a
-// store — the kernel then runs at HBM speed.  Pixels of the remaining tiles whose depth falls into a
-// candidate's depth interval are transformed and tested exactly as in k_self_filter_depth (same
-// rounding, same verdict).
-#define TGT_W 32
-#define TGT_H 16
-
-#define TGT_PER_WARP 5  // tiles per warp: the depth of tile i + 1 is in flight while tile i is processed
-
-__device__ __forceinline__ void tgt_load(const float* __restrict__ img, int H, int W, int tile, int tiles_x, int ntiles, int lane,
-                                         float4 (&d)[4]) {
-  const int ty0 = tile / tiles_x, tx0 = tile - ty0 * tiles_x;
-  const int u = tx0 * TGT_W + 4 * (lane & 7), vb = ty0 * TGT_H + (lane >> 3);
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const int v = vb + 4 * j;
-    d[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (tile < ntiles && v < H && u < W) d[j] = __ldcs(reinterpret_cast<const float4*>(img + (size_t)v * W + u));
-  }
-}
-
-__global__ void __launch_bounds__(TGF_BLOCK, 3)
-k_self_filter_tiles(const float* __restrict__ depth, const TgFilterState* __restrict__ prep, TgDepthParams p, float radius,
-                    uint8_t* __restrict__ mask) {
-  __shared__ TgFilterState st;
-  const int s = blockIdx.y;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int tiles_x = (p.W + TGT_W - 1) / TGT_W, tiles_y = (p.H + TGT_H - 1) / TGT_H, ntiles = tiles_x * tiles_y;
-  const int tile0 = blockIdx.x * (TGF_BLOCK / 32) * TGT_PER_WARP + warp;  // this warp: tile0, tile0 + 8, ...
-  const float* img = depth + (size_t)s * p.H * p.W;
-  uint8_t* mrow = mask + (size_t)s * p.H * p.W;
-  float4 dn[4];
-  tgt_load(img, p.H, p.W, tile0, tiles_x, ntiles, lane, dn);  // first tile's depth is in flight during the state load
-  {
-    const float* src = reinterpret_cast<const float*>(prep + s);
-    float* dst = reinterpret_cast<float*>(&st);
-    for (int j = threadIdx.x; j < (int)(sizeof(TgFilterState) / 4); j += TGF_BLOCK) dst[j] = __ldg(src + j);
-  }
-  __syncthreads();
-  const float rp = radius + 2e-3f;
-  const float ifx = (float)(1.0 / p.fx), ify = (float)(1.0 / p.fy), cxf = (float)p.cx, cyf = (float)p.cy;
-  const int tx = lane & 7, tyy = lane >> 3;
-  for (int it = 0; it < TGT_PER_WARP; ++it) {
-    const int tile = tile0 + it * (TGF_BLOCK / 32);
-    if (tile >= ntiles) break;  // warp-uniform
-    float z[16];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      z[4 * j] = dn[j].x; z[4 * j + 1] = dn[j].y; z[4 * j + 2] = dn[j].z; z[4 * j + 3] = dn[j].w;
-    }
-    if (it + 1 < TGT_PER_WARP) tgt_load(img, p.H, p.W, tile + TGF_BLOCK / 32, tiles_x, ntiles, lane, dn);
-    const int ty0 = tile / tiles_x, tx0 = tile - ty0 * tiles_x;
-    const int u0 = tx0 * TGT_W, v0 = ty0 * TGT_H, u = u0 + 4 * tx;
-    // candidate spheres of the tile (skipped when the tile misses the robot's image-space box)
-    uint32_t m[4] = {0u, 0u, 0u, 0u};
-    if ((float)(u0 + TGT_W) >= st.img_box[0] && (float)u0 <= st.img_box[2] && (float)(v0 + TGT_H) >= st.img_box[1] &&
-        (float)v0 <= st.img_box[3]) {
-      const float a0 = ((float)u0 - 0.5f - cxf) * ifx, a1 = ((float)(u0 + TGT_W) - 0.5f - cxf) * ifx;
-      const float b0 = ((float)v0 - 0.5f - cyf) * ify, b1 = ((float)(v0 + TGT_H) - 0.5f - cyf) * ify;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int j = lane + 32 * q;
-        bool c = false;
-        if (j < TGM_N_SPHERES) {
-          const float X = st.cc[3 * j], Y = st.cc[3 * j + 1], Z = st.cc[3 * j + 2];
-          const float zl = fmaxf(fmaxf(Z - rp, p.zmin - 1e-3f), 0.f), zh = fminf(Z + rp, p.zmax + 1e-3f);
-          if (zl <= zh) {
-            const float xmin = (a0 >= 0.f ? zl : zh) * a0, xmax = (a1 >= 0.f ? zh : zl) * a1;
-            const float ymin = (b0 >= 0.f ? zl : zh) * b0, ymax = (b1 >= 0.f ? zh : zl) * b1;
-            c = xmin <= X + rp && xmax >= X - rp && ymin <= Y + rp && ymax >= Y - rp;
-          }
-        }
-        m[q] = __ballot_sync(0xffffffffu, c);
-      }
-    }
-    // validity: NaN fails every compare and -inf fails z > 0 exactly like np.nan_to_num's 0 / -FLT_MAX;
-    // +inf behaves like +FLT_MAX against any zmax
-    uint32_t ok = 0;
-#pragma unroll
-    for (int k = 0; k < 16; ++k)
-      if (z[k] > 0.f && z[k] >= p.zmin && z[k] <= p.zmax) ok |= 1u << k;
-    if ((m[0] | m[1] | m[2] | m[3]) != 0u) {  // warp-uniform: the robot may be visible in this tile
-      uint32_t cand = 0;  // pixels whose depth lies in some candidate sphere's depth interval
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint32_t bits = m[q];
-        while (bits) {
-          const int j = 32 * q + __ffs(bits) - 1;
-          bits &= bits - 1;
-          const float Z = st.cc[3 * j + 2];
-#pragma unroll
-          for (int k = 0; k < 16; ++k) cand |= (fabsf(z[k] - Z) < rp ? 1u : 0u) << k;
-        }
-      }
-      cand &= ok;
-      while (cand) {  // rare: exact transform + exact test, same arithmetic as the generic kernel
-        const int k = __ffs(cand) - 1;
-        cand &= cand - 1;
-        const int uu = u + (k & 3), vv = v0 + tyy + 4 * (k >> 2);
-        float zz = 0.f;
-#pragma unroll
-        for (int kk = 0; kk < 16; ++kk)
-          if (kk == k) zz = z[kk];  // register select: keeps z[] out of local memory
-        if (isinf(zz)) zz = 3.4028234663852886e38f;  // np.nan_to_num (only reachable with zmax = inf)
-        const float xc = (float)((((double)(float)uu - p.cx) * (double)zz) / p.fx);
-        const float yc = (float)((((double)(float)vv - p.cy) * (double)zz) / p.fy);
-        const float wx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[0]), __fmul_rn(yc, st.cam_r[1])), __fmul_rn(zz, st.cam_r[2])), st.cam_t[0]);
-        const float wy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[3]), __fmul_rn(yc, st.cam_r[4])), __fmul_rn(zz, st.cam_r[5])), st.cam_t[1]);
-        const float wz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(xc, st.cam_r[6]), __fmul_rn(yc, st.cam_r[7])), __fmul_rn(zz, st.cam_r[8])), st.cam_t[2]);
-        bool inside = false;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint32_t bits = m[q];
-          while (bits) {
-            const int j = 32 * q + __ffs(bits) - 1;
-            bits &= bits - 1;
-            const float dx = __fsub_rn(wx, st.c[3 * j]), dy = __fsub_rn(wy, st.c[3 * j + 1]), dz = __fsub_rn(wz, st.c[3 * j + 2]);
-            const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-            inside |= d2 < p.r2;
-          }
-        }
-        if (inside) ok &= ~(1u << k);
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int v = v0 + tyy + 4 * j;
-      if (v < p.H && u < p.W) {
-        const uint32_t b = (ok >> (4 * j)) & 0xFu;
-        __stcs(reinterpret_cast<uint32_t*>(mrow + (size_t)v * p.W + u), (b & 1u) | ((b & 2u) << 7) | ((b & 4u) << 14) | ((b & 8u) << 21));
-      }
-    }
-  }
-}
-
 // ---- K4 v3: streaming fast path (full-resolution frames, mask only) --------------------------------
 // Persistent blocks, two per SM.  A block owns a contiguous range of "chunks" (R full image rows of one
 // state = one contiguous piece of the depth array) and pulls them through a 4-stage shared-memory ring
@@ -405,7 +265,7 @@ k_self_filter_tiles(const float* __restrict__ depth, const TgFilterState* __rest
 #define TGS_STAGES 4
 #endif
 #ifndef TGS_STAGE_BYTES
-#define TGS_STAGE_BYTES 24576
+#define TGS_STAGE_BYTES 20480
 #endif
 #ifndef TGS_MAX_ROWS
 #define TGS_MAX_ROWS 8
@@ -437,13 +297,21 @@ __device__ __forceinline__ void tg_mbar_wait(uint32_t bar_addr, uint32_t parity,
   while (!tg_mbar_try(bar_addr, parity)) __nanosleep(backoff_ns);
 }
 
+#ifndef TGS_CONSUMERS
 #define TGS_CONSUMERS 8                         // consumer warps; warp TGS_CONSUMERS is the producer
+#endif
+#ifndef TGS_BLOCKS_PER_SM
+#define TGS_BLOCKS_PER_SM 2
+#endif
 #define TGS_THREADS ((TGS_CONSUMERS + 1) * 32)
 #define TGS_STATE_BYTES ((int)((sizeof(TgFilterState) + 127) / 128 * 128))
-#define TGS_SLOT_BYTES (TGS_STAGE_BYTES + TGS_STATE_BYTES)  // one ring slot = the chunk's depth rows + its robot state
+#define TGS_LIST_BYTES (112 * 16)               // band list: (X, Y, Z, sphere index) of the spheres that can meet the chunk's rows
+#define TGS_META_BYTES 128                      // {count, first tile column, last tile column}
+// one ring slot = the chunk's depth rows + its robot state + the chunk's band list
+#define TGS_SLOT_BYTES (TGS_STAGE_BYTES + TGS_STATE_BYTES + TGS_LIST_BYTES + TGS_META_BYTES)
 static_assert(sizeof(TgFilterState) % 16 == 0, "bulk copies move multiples of 16 bytes");
 
-__global__ void __launch_bounds__(TGS_THREADS, 2)
+__global__ void __launch_bounds__(TGS_THREADS, TGS_BLOCKS_PER_SM)
 k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __restrict__ prep, TgDepthParams p, float radius,
                      uint8_t* __restrict__ mask, int R, int cpf, int total_chunks) {
   extern __shared__ __align__(128) unsigned char tgs_smem[];
@@ -457,28 +325,84 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
   const int dS = G / cpf, dK = G - dS * cpf;
   int s = (int)blockIdx.x / cpf, kc = (int)blockIdx.x - s * cpf;  // state and chunk-in-frame of chunk i, kept incrementally
   const int W = p.W, H = p.H, w4 = W >> 2, ntx = (W + 31) >> 5;
+  const float rp = radius + 2e-3f;
+  const float ifx = (float)(1.0 / p.fx), ify = (float)(1.0 / p.fy), cxf = (float)p.cx, cyf = (float)p.cy;
   if (tid == 0) {
 #pragma unroll
     for (int k = 0; k < TGS_STAGES; ++k) {
-      tg_mbar_init(bars + k, 1);
+      tg_mbar_init(bars + k, 2);  // expect_tx arrival (copies) + list arrival
       tg_mbar_init(bars + TGS_STAGES + k, TGS_CONSUMERS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if (warp == TGS_CONSUMERS) {  // ---- producer: one thread keeps TGS_STAGES slots in flight
-    if (lane != 0) return;
+  if (warp == TGS_CONSUMERS) {
+    // ---- producer warp: keeps TGS_STAGES slots in flight (lane 0 issues the bulk copies) and, while the copies
+    // fly, writes the slot's band list: the spheres whose depth interval x projected box can meet the chunk's rows,
+    // with the tile columns they span.  Consumers only ever look at that list.
     uint64_t stream_once, keep;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(stream_once));
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
+    const float fxf = (float)p.fx;
     for (int i = 0, slot = 0, round = 0; i < n; ++i) {
       if (round > 0) tg_mbar_wait(empty0 + 8 * slot, (uint32_t)(round - 1) & 1u, 200);
       const int row0 = kc * R, rows = min(R, H - row0);
       const uint32_t bytes = (uint32_t)rows * (uint32_t)W * 4u;
       unsigned char* dst = tgs_smem + (size_t)slot * TGS_SLOT_BYTES;
-      tg_mbar_expect_tx(bars + slot, bytes + (uint32_t)sizeof(TgFilterState));
-      tg_bulk_g2s(dst, depth + ((size_t)s * H + row0) * W, bytes, bars + slot, stream_once);
-      tg_bulk_g2s(dst + TGS_STAGE_BYTES, prep + s, (uint32_t)sizeof(TgFilterState), bars + slot, keep);
+      if (lane == 0) {
+        tg_mbar_expect_tx(bars + slot, bytes + (uint32_t)sizeof(TgFilterState));
+        tg_bulk_g2s(dst, depth + ((size_t)s * H + row0) * W, bytes, bars + slot, stream_once);
+        tg_bulk_g2s(dst + TGS_STAGE_BYTES, prep + s, (uint32_t)sizeof(TgFilterState), bars + slot, keep);
+      }
+      const TgFilterState* ps = prep + s;
+      float4* list = reinterpret_cast<float4*>(dst + TGS_STAGE_BYTES + TGS_STATE_BYTES);
+      int cnt = 0;
+      float ulo = INFINITY, uhi = -INFINITY;
+      if ((float)(row0 + rows) >= __ldg(&ps->img_box[1]) && (float)row0 <= __ldg(&ps->img_box[3])) {  // warp-uniform
+        const float b0 = ((float)row0 - 0.5f - cyf) * ify, b1 = ((float)(row0 + rows) - 0.5f - cyf) * ify;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int j = lane + 32 * q;
+          bool c = false;
+          float X = 0.f, Y = 0.f, Z = 0.f;
+          if (j < TGM_N_SPHERES) {
+            X = __ldg(&ps->cc[3 * j]); Y = __ldg(&ps->cc[3 * j + 1]); Z = __ldg(&ps->cc[3 * j + 2]);
+            const float zl = fmaxf(fmaxf(Z - rp, p.zmin - 1e-3f), 0.f), zh = fminf(Z + rp, p.zmax + 1e-3f);
+            if (zl <= zh) {
+              const float ymin = (b0 >= 0.f ? zl : zh) * b0, ymax = (b1 >= 0.f ? zh : zl) * b1;
+              c = ymin <= Y + rp && ymax >= Y - rp;
+              if (c) {  // image columns the sphere can cover (as k_filter_prepare's img_box)
+                if (zl < 0.01f) {
+                  ulo = -INFINITY; uhi = INFINITY;
+                } else {
+                  const float xa = X - rp, xb = X + rp;
+                  ulo = fminf(ulo, cxf + fxf * (xa >= 0.f ? xa / zh : xa / zl) - 1.5f);
+                  uhi = fmaxf(uhi, cxf + fxf * (xb >= 0.f ? xb / zl : xb / zh) + 1.5f);
+                }
+              }
+            }
+          }
+          const uint32_t bq = __ballot_sync(0xffffffffu, c);
+          if (c) list[cnt + __popc(bq & ((1u << lane) - 1u))] = make_float4(X, Y, Z, __int_as_float(j));
+          cnt += __popc(bq);
+        }
+#pragma unroll
+        for (int of = 16; of; of >>= 1) {
+          ulo = fminf(ulo, __shfl_xor_sync(0xffffffffu, ulo, of));
+          uhi = fmaxf(uhi, __shfl_xor_sync(0xffffffffu, uhi, of));
+        }
+      }
+      if (lane == 0) {  // float -> int conversion saturates, +-inf are fine
+        int4 meta;
+        meta.x = cnt;
+        meta.y = cnt ? (int)floorf(ulo) : 0x7fffffff;  // pixel columns the band's spheres can cover
+        meta.z = cnt ? (int)ceilf(uhi) : -0x7fffffff;
+        meta.w = 0;
+        *reinterpret_cast<int4*>(dst + TGS_STAGE_BYTES + TGS_STATE_BYTES + TGS_LIST_BYTES) = meta;
+      }
+      __syncwarp();
+      // second arrival on the full barrier (count 2): releases the list and the meta to the consumers
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(full0 + 8 * slot) : "memory");
       s += dS; kc += dK;
       if (kc >= cpf) { kc -= cpf; ++s; }
       if (++slot == TGS_STAGES) { slot = 0; ++round; }
@@ -489,48 +413,49 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
   // a point can only be inside a sphere of radius r if its camera-frame distance to the centre is below
   // r + 2 mm, and it surely is if that distance is below r - 2 mm: the camera-frame and the world-frame
   // arithmetic differ by rounding only (< 2e-5 m for |p| < 10 m).  The shell between is settled exactly.
-  const float rp = radius + 2e-3f, rout2 = rp * rp;
+  const float rout2 = rp * rp;
   const float rin = fmaxf(radius - 2e-3f, 0.f), rin2 = rin * rin;
-  const float ifx = (float)(1.0 / p.fx), ify = (float)(1.0 / p.fy), cxf = (float)p.cx, cyf = (float)p.cy;
   // z > 0 && z >= zmin  <=>  z >= max(zmin, smallest positive float); NaN fails every compare and -inf fails z > 0
   // exactly like np.nan_to_num's 0 / -FLT_MAX; +inf behaves like +FLT_MAX against any zmax
-  const float zlo_ok = p.zmin > 0.f ? p.zmin : 1.401298464e-45f, zhi_ok = p.zmax;
+  const uint32_t ok_lo = __float_as_uint(p.zmin > 0.f ? p.zmin : 1.401298464e-45f);
+  const uint32_t ok_span = __float_as_uint(p.zmax) - ok_lo;  // the host only takes this path when zmax >= lo
   const int lc = lane & 7, lr = lane >> 3;
   for (int i = 0, slot = 0, round = 0; i < n; ++i) {
-    const int row0 = kc * R, rows = min(R, H - row0), nty = (rows + 3) >> 2;
+    const int row0 = kc * R, rows = min(R, H - row0);
     const unsigned char* base = tgs_smem + (size_t)slot * TGS_SLOT_BYTES;
     const float4* buf = reinterpret_cast<const float4*>(base);
     const TgFilterState& st = *reinterpret_cast<const TgFilterState*>(base + TGS_STAGE_BYTES);
+    const float4* list = reinterpret_cast<const float4*>(base + TGS_STAGE_BYTES + TGS_STATE_BYTES);
     uint32_t* mrow = reinterpret_cast<uint32_t*>(mask + ((size_t)s * H + row0) * W);
     tg_mbar_wait(full0 + 8 * slot, (uint32_t)round & 1u, 40);
-    // tile columns that meet the robot's image-space box (float -> int conversion saturates, +-inf are fine)
-    int tx_lo = 0x7fffffff, tx_hi = -1;
-    if ((float)(row0 + rows) >= st.img_box[1] && (float)row0 <= st.img_box[3]) {
-      tx_lo = (int)fmaxf(ceilf((st.img_box[0] - 32.f) * 0.03125f), 0.f);
-      tx_hi = (int)fminf(floorf(st.img_box[2] * 0.03125f), (float)ntx);
-    }
+    const int4 meta = *reinterpret_cast<const int4*>(base + TGS_STAGE_BYTES + TGS_STATE_BYTES + TGS_LIST_BYTES);
+    const int cnt = meta.x, u_lo = meta.y, u_hi = meta.z, nq = (cnt + 31) >> 5;
+    // one warp = one tile of 32 x 4 pixels; lane = 4 consecutive pixels (one float4) of row 4 ty + lr.  Compact tiles
+    // keep the candidate lists short (128 x 1 strips were 25 % slower).
+    const int nty = (rows + 3) >> 2;
     int tx = warp, ty = 0;
     while (tx >= ntx) { tx -= ntx; ++ty; }
-    while (ty < nty) {  // one warp = one tile of 32 x 4 pixels; lane = 4 consecutive pixels of row 4 ty + lr
-      const int c4 = 8 * tx + lc, rr = 4 * ty + lr;
-      const int f = rr * w4 + c4;  // float4 index in the chunk = uint32 index in the chunk's mask rows
-      const bool have = c4 < w4 && rr < rows;
+    while (ty < nty) {
+      const int c4 = 8 * tx + lc, rl = 4 * ty + lr;
+      const int f = rl * w4 + c4;  // float4 index in the chunk = uint32 index in the chunk's mask rows
+      const bool have = c4 < w4 && rl < rows;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (have) v = buf[f];
       const float z[4] = {v.x, v.y, v.z, v.w};
-      uint32_t ok = 0;
+      // z in [lo, hi] with lo > 0: positive floats order like their bit patterns, everything else (negative, -0, NaN)
+      // wraps to a huge unsigned difference -> one subtract + one unsigned compare per pixel
+      uint32_t okb = 0;  // mask bytes of the 4 pixels
 #pragma unroll
-      for (int k = 0; k < 4; ++k) ok |= (z[k] >= zlo_ok && z[k] <= zhi_ok ? 1u : 0u) << k;
-      if (tx >= tx_lo && tx <= tx_hi) {  // warp-uniform
-        float zlo = INFINITY, zhi = -INFINITY;  // depth range of the tile's valid pixels
+      for (int k = 0; k < 4; ++k) okb |= (__float_as_uint(z[k]) - ok_lo <= ok_span ? 1u : 0u) << (8 * k);
+      if (cnt != 0 && 32 * tx + 31 >= u_lo && 32 * tx <= u_hi) {  // warp-uniform: a band sphere reaches these columns
+        uint32_t ok = (okb & 1u) | (okb >> 7 & 2u) | (okb >> 14 & 4u) | (okb >> 21 & 8u);
+        // depth range of the tile's valid pixels: positive floats order like their bit patterns -> one REDUX each
+        uint32_t lo_b = 0x7f800000u, hi_b = 0u;
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          if (ok >> k & 1u) { zlo = fminf(zlo, z[k]); zhi = fmaxf(zhi, z[k]); }
-#pragma unroll
-        for (int of = 16; of; of >>= 1) {
-          zlo = fminf(zlo, __shfl_xor_sync(0xffffffffu, zlo, of));
-          zhi = fmaxf(zhi, __shfl_xor_sync(0xffffffffu, zhi, of));
-        }
+          if (ok >> k & 1u) { lo_b = min(lo_b, __float_as_uint(z[k])); hi_b = max(hi_b, __float_as_uint(z[k])); }
+        const float zlo = __uint_as_float(__reduce_min_sync(0xffffffffu, lo_b));
+        const float zhi = __uint_as_float(__reduce_max_sync(0xffffffffu, hi_b));
         uint32_t m[4] = {0u, 0u, 0u, 0u};
         if (zlo <= zhi) {
           // candidate spheres: depth interval meets the tile's depth range and, over that depth range, the tile's
@@ -540,22 +465,23 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
           const float b0 = ((float)v0 - 0.5f - cyf) * ify, b1 = ((float)(v0 + 4) - 0.5f - cyf) * ify;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
-            const int j = lane + 32 * q;
-            bool c = false;
-            if (j < TGM_N_SPHERES) {
-              const float X = st.cc[3 * j], Y = st.cc[3 * j + 1], Z = st.cc[3 * j + 2];
-              const float zl = fmaxf(Z - rp, zlo), zh = fminf(Z + rp, zhi);
-              if (zl <= zh) {
-                const float xmin = (a0 >= 0.f ? zl : zh) * a0, xmax = (a1 >= 0.f ? zh : zl) * a1;
-                const float ymin = (b0 >= 0.f ? zl : zh) * b0, ymax = (b1 >= 0.f ? zh : zl) * b1;
-                c = xmin <= X + rp && xmax >= X - rp && ymin <= Y + rp && ymax >= Y - rp;
+            if (q < nq) {  // warp-uniform
+              bool c = false;
+              if (lane + 32 * q < cnt) {
+                const float4 e = list[lane + 32 * q];
+                const float zl = fmaxf(e.z - rp, zlo), zh = fminf(e.z + rp, zhi);
+                if (zl <= zh) {
+                  const float xmin = (a0 >= 0.f ? zl : zh) * a0, xmax = (a1 >= 0.f ? zh : zl) * a1;
+                  const float ymin = (b0 >= 0.f ? zl : zh) * b0, ymax = (b1 >= 0.f ? zh : zl) * b1;
+                  c = xmin <= e.x + rp && xmax >= e.x - rp && ymin <= e.y + rp && ymax >= e.y - rp;
+                }
               }
+              m[q] = __ballot_sync(0xffffffffu, c);
             }
-            m[q] = __ballot_sync(0xffffffffu, c);
           }
         }
         if ((m[0] | m[1] | m[2] | m[3]) != 0u) {  // warp-uniform: the robot may be visible in this tile
-          const float ay = ((float)(row0 + rr) - cyf) * ify;
+          const float ay = ((float)(row0 + rl) - cyf) * ify;
           float ax[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) ax[k] = ((float)(4 * c4 + k) - cxf) * ifx;
@@ -564,12 +490,11 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
           for (int q = 0; q < 4; ++q) {
             uint32_t bits = m[q];
             while (bits) {
-              const int j = 32 * q + __ffs(bits) - 1;
+              const float4 e = list[32 * q + __ffs(bits) - 1];
               bits &= bits - 1;
-              const float X = st.cc[3 * j], Y = st.cc[3 * j + 1], Z = st.cc[3 * j + 2];
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                const float dx = fmaf(z[k], ax[k], -X), dy = fmaf(z[k], ay, -Y), dz = z[k] - Z;
+                const float dx = fmaf(z[k], ax[k], -e.x), dy = fmaf(z[k], ay, -e.y), dz = z[k] - e.z;
                 const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
                 inside |= (d2 < rin2 ? 1u : 0u) << k;
                 shell |= (d2 < rout2 ? 1u : 0u) << k;
@@ -581,7 +506,7 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
           while (need) {  // rare (2 mm shells): exact transform + exact test, same arithmetic as the generic kernel
             const int k = __ffs(need) - 1;
             need &= need - 1;
-            const int uu = 4 * c4 + k, vv = row0 + rr;
+            const int uu = 4 * c4 + k, vv = row0 + rl;
             float zz = k == 0 ? z[0] : k == 1 ? z[1] : k == 2 ? z[2] : z[3];
             if (isinf(zz)) zz = 3.4028234663852886e38f;  // np.nan_to_num (only reachable with zmax = inf)
             const float xc = (float)((((double)(float)uu - p.cx) * (double)zz) / p.fx);
@@ -594,7 +519,7 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
             for (int q = 0; q < 4; ++q) {
               uint32_t bits = m[q];
               while (bits) {
-                const int j = 32 * q + __ffs(bits) - 1;
+                const int j = __float_as_int(list[32 * q + __ffs(bits) - 1].w);
                 bits &= bits - 1;
                 const float dx = __fsub_rn(wx, st.c[3 * j]), dy = __fsub_rn(wy, st.c[3 * j + 1]), dz = __fsub_rn(wz, st.c[3 * j + 2]);
                 const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
@@ -604,9 +529,9 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
             if (in) ok &= ~(1u << k);
           }
         }
+        okb = (ok * 0x00204081u) & 0x01010101u;  // bit k of ok lands on bit 8k (k + 7k) of the product, no carries
       }
-      // 4 mask bytes from 4 bits: bit k of ok lands on bit 8k (k + 7k) of the product, no carries
-      if (have) __stcs(mrow + f, (ok * 0x00204081u) & 0x01010101u);
+      if (have) __stcs(mrow + f, okb);
       tx += TGS_CONSUMERS;
       while (tx >= ntx) { tx -= ntx; ++ty; }
     }
@@ -638,9 +563,8 @@ extern "C" int tg_self_filter_depth(const float* depth, int H, int W, int stride
   TG_CUDA(cudaMallocAsync(&prep, sizeof(TgFilterState) * (size_t)S, st));
   k_filter_prepare<<<tg_div_up(S, 4), 128, 0, st>>>(states, (int)S, radius, p, prep);
   const int npx = p.Hs * p.Ws;
-#ifndef TG_K4_TILES
   if (stride == 1 && world == nullptr && (W & 3) == 0 && ((uintptr_t)mask & 3) == 0 && W * 4 <= TGS_STAGE_BYTES &&
-      (long long)S * H < (1ll << 28)) {
+      (long long)S * H < (1ll << 28) && zmax >= (zmin > 0.f ? zmin : 1.401298464e-45f)) {
     static bool attr_set[64] = {};
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -653,14 +577,8 @@ extern "C" int tg_self_filter_depth(const float* depth, int H, int W, int stride
     const int R = min(TGS_MAX_ROWS, TGS_STAGE_BYTES / (W * 4));
     const int cpf = tg_div_up(H, R);
     const int total = cpf * (int)S;
-    const int blocks = min(sms * 2, total);
+    const int blocks = min(sms * TGS_BLOCKS_PER_SM, total);
     k_self_filter_stream<<<blocks, TGS_THREADS, smem, st>>>(depth, prep, p, radius, mask, R, cpf, total);
-  } else
-#endif
-  if (stride == 1 && world == nullptr && (W & 3) == 0 && ((uintptr_t)mask & 3) == 0) {
-    const int tiles = tg_div_up(W, TGT_W) * tg_div_up(H, TGT_H);
-    dim3 grid(tg_div_up(tiles, (TGF_BLOCK / 32) * TGT_PER_WARP), (unsigned)S);
-    k_self_filter_tiles<<<grid, TGF_BLOCK, 0, st>>>(depth, prep, p, radius, mask);
   } else {
     dim3 grid(tg_div_up(npx, TGF_BLOCK * 4), (unsigned)S);
     k_self_filter_depth<4><<<grid, TGF_BLOCK, 0, st>>>(depth, prep, p, mask, world);

@@ -192,6 +192,27 @@ int tg_carve_flags(const float* points, int64_t N, int mode, const double* K, co
                    float zmin, float zmax, int width, int height, const float* depth,
                    float merge_radius, uint8_t* keep, void* stream);
 
+/* ---- callers next to the path --------------------------- */
+/* fp64 FK: q10 DEVICE S x 10 (torso, 7 arm joints, head pan, head tilt) -> frames DEVICE
+ * S x 15 x 12 (3x4 row-major, base_link frame).  Replaces kinematics/fetch/fk_numpy.py:32-157
+ * for the occlusion check below.                                                        */
+int tg_fk_frames_f64(const double* q10, int64_t S, double* frames, void* stream);
+/* Batched self-occlusion check: replaces checker/occlusion.py:48-116
+ * (check_self_occlusion(link_poses, target_center, target_radius, intrinsics, image_shape)).
+ * occluded[s] = 1 iff the cv2.circle discs of the robot spheres and of the target sphere
+ * share a pixel of the H x W image.  target DEVICE n_targets x 4 f64 (x, y, z, r in
+ * base_link; n_targets = 1 or S), K HOST 3x3 f64.  `links_present` bit i = link i of the
+ * 15-link table is in the caller's dict (missing head_tilt_link -> 0 everywhere).       */
+int tg_check_occlusion_frames(const double* frames, uint32_t links_present, const double* target,
+                              int64_t n_targets, int64_t S, const double* K, int H, int W,
+                              uint8_t* occluded, void* stream);
+int tg_check_occlusion(const double* q10, const double* target, int64_t n_targets, int64_t S,
+                       const double* K, int H, int W, uint8_t* occluded, void* stream);
+/* first[g] = index within group g (consecutive `group` entries of valid[B]) of the first
+ * non-zero verdict, or -1: the serial "first grasp x IK attempt that passes" of
+ * subgoal_generator/samplers/grasp_sampler.py:109-137 after one tg_check_configs call.  */
+int tg_first_valid(const uint8_t* valid, int64_t B, int group, int32_t* first, void* stream);
+
 /* ---- synthetic input (benchmark support, not part of the reference surface) ----- */
 /* Analytic head-camera depth frames: rays against the 8 x 6 x 2.6 m room shell, `nb`
  * furniture boxes (DEVICE nb x 6: lo xyz, hi xyz; nb <= 64) and the robot's own 111

@@ -128,3 +128,38 @@ def test_oracle_degenerate_clouds(n):
     assert cl.shape == (8,)
     if n == 0:
         assert np.all(np.isinf(cl))
+
+
+def test_occlusion_oracle_matches_reference_golden(golden):
+    """oracle/occlusion.py vs the unmodified reference's check_self_occlusion (cv2 discs) on seeded states:
+    tools/make_golden_occlusion.py; a sample here, the GPU test runs all of them."""
+    from oracle import occlusion as oocc
+
+    g = golden("occlusion.npz")
+    K, shape = g["K"], tuple(int(v) for v in g["shape"])
+    pos = np.nonzero(g["occluded"])[0][:12]
+    neg = np.nonzero(~g["occluded"])[0][:12]
+    for i in np.concatenate([pos, neg]):
+        assert oocc.check_self_occlusion(g["q10"][i], g["target"][i], float(g["radius"][i]), K, shape) == bool(g["occluded"][i])
+    Ks, ss = g["K_small"], tuple(int(v) for v in g["shape_small"])
+    for i in range(24):
+        assert oocc.check_self_occlusion(g["q10"][i], g["target"][i], float(g["radius"][i]), Ks, ss) == bool(g["occluded_small"][i])
+
+
+def test_disc_rasteriser_known_answer_and_cv2():
+    """cv2.circle(mask, c, 5, 1, -1) fills rows of half-width 5,4,4,4,3,0 (81 pixels) — checked against cv2 itself
+    wherever cv2 is importable (build container)."""
+    from oracle import occlusion as oocc
+
+    assert list(oocc.disc_half_widths(5)) == [5, 4, 4, 4, 3, 0]
+    m = np.zeros((20, 20), np.uint8)
+    oocc.draw_disc(m, 10, 10, 5)
+    assert m.sum() == 81
+    cv2 = pytest.importorskip("cv2")
+    for r in (1, 2, 3, 7, 31, 64, 200):
+        for c in ((40, 30), (2, 58), (79, 0)):
+            ref = np.zeros((60, 80), np.uint8)
+            cv2.circle(ref, c, r, 1, -1)
+            got = np.zeros((60, 80), np.uint8)
+            oocc.draw_disc(got, c[0], c[1], r)
+            assert np.array_equal(ref, got)

@@ -43,4 +43,12 @@ def __getattr__(name):  # lazy: torch / CUDA only when the engine is touched
         from . import scene
 
         return getattr(scene, name)
+    if name in ("check_self_occlusion", "check_self_occlusion_batch"):
+        from . import occlusion
+
+        return getattr(occlusion, name)
+    if name in ("BatchedGraspValidator", "validate_grasp_candidates", "first_valid"):
+        from . import grasp
+
+        return getattr(grasp, name)
     raise AttributeError(name)

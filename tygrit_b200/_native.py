@@ -71,6 +71,15 @@ _SIGS = {
         [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p,
          C.c_float, C.c_void_p, C.c_void_p],
     ),
+    "tg_fk_frames_f64": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "tg_check_occlusion_frames": (
+        C.c_int,
+        [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
+    ),
+    "tg_check_occlusion": (
+        C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    ),
+    "tg_first_valid": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]),
     "tg_synth_depth": (
         C.c_int,
         [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float, C.c_uint64, C.c_void_p,

@@ -107,7 +107,7 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
       TgClass cl;
       tg_class_clear(cl);
       if (live) {
-        cfg[0] = __ldg(base + 3 * (size_t)i); cfg[1] = __ldg(base + 3 * (size_t)i + 1); cfg[2] = __ldg(base + 3 * (size_t)i + 2);
+        cfg[0] = __ldcs(base + 3 * (size_t)i); cfg[1] = __ldcs(base + 3 * (size_t)i + 1); cfg[2] = __ldcs(base + 3 * (size_t)i + 2);
         if (!g.empty) {
           const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
           tg_stage_a(g, thr, p, cl);
@@ -123,8 +123,8 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
         if (lane == 0) pos = atomicAdd(&s_tail, (unsigned)__popc(m));
         pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
         if (surv) {
-          const float4 a0 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i);
-          const float4 a1 = __ldg(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i + 1);
+          const float4 a0 = __ldcs(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i);
+          const float4 a1 = __ldcs(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i + 1);
           const unsigned sl = pos & (TGC_RING - 1);
           ring.cfg[0][sl] = cfg[0]; ring.cfg[1][sl] = cfg[1]; ring.cfg[2][sl] = cfg[2];
           ring.cfg[3][sl] = a0.x; ring.cfg[4][sl] = a0.y; ring.cfg[5][sl] = a0.z; ring.cfg[6][sl] = a0.w;

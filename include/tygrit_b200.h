@@ -144,6 +144,9 @@ int tg_debug_stats(int64_t* out16, int reset);
  * events on the launching stream.  tg_env_timing_read waits for them and returns
  * {phase-1 ms, phase-2 ms, launch pairs} accumulated since the last read (HOST out, 3 doubles). */
 int tg_env_set_timing(tg_env* env, int on);
+/* Test hook: use only the first `items` entries of the ambiguous queue (0 = all) so that the
+ * overflow path (items resolved inline by their own lane) can be exercised with small batches. */
+int tg_env_set_queue_limit(tg_env* env, int64_t items);
 int tg_env_timing_read(tg_env* env, double* out3);
 
 /* ---- robot self-filter (kinematics/robot_filter.py:13-64) ---------------------- */

@@ -105,6 +105,30 @@ def test_room_configs_vs_c_oracle(room):
     assert 0.05 < valid.mean() < 0.6
 
 
+def test_queue_overflow_resolves_inline_with_same_verdicts(room):
+    """A launch pair takes up to 32 Mi configurations against an 8 Mi-item queue; items that do not fit are resolved
+    inline by their own lane.  Shrink the queue (test hook) so that most items overflow: verdicts and edge verdicts must
+    not change, and the overflow counter must say the path ran."""
+    cloud, w, cc = room
+    arm, base = synth.random_configs(60_000, seed=17)
+    a0, b0, a1, b1 = synth.random_edges(2_000, seed=18)
+    w.counters()
+    want = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    want_e = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1)).cpu().numpy()
+    assert w.counters()["overflow_inline"] == 0
+    try:
+        w.set_queue_limit(64)
+        got = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+        c = w.counters()
+        got_e = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1)).cpu().numpy()
+        assert c["overflow_inline"] > 100
+        assert w.counters()["overflow_inline"] > 100
+    finally:
+        w.set_queue_limit(0)
+    assert np.array_equal(got, want) and np.array_equal(got_e, want_e)
+    _assert_verdicts(got, cc.clearance(arm, base), "overflow")
+
+
 def test_ragged_and_degenerate_batches(room):
     cloud, w, cc = room
     arm, base = synth.random_configs(1000, seed=3)

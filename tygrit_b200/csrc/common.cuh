@@ -142,6 +142,7 @@ struct tg_env {
   TgItem* items;
   unsigned* queue_count;
   unsigned queue_capacity;
+  unsigned queue_limit;  // test hook: 0 = use the whole queue
   TgCounters* counters_dev;
   TgCounters* counters_host;  // pinned
   int64_t launches;

@@ -418,7 +418,7 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
   TG_CUDA(cudaMallocHost(&env->header_host, TG_HEADER_BYTES));
   TG_CUDA(cudaMalloc(&env->extras_dev, sizeof(TgExtras)));
   TG_CUDA(cudaMemset(env->extras_dev, 0, sizeof(TgExtras)));
-  env->queue_capacity = 1u << 22;  // 4M items = 256 MB
+  env->queue_capacity = 1u << 23;  // 8 Mi items = 512 MB (two halves for the host pipeline, one piece for the device API)
   TG_CUDA(cudaMalloc(&env->items, (size_t)env->queue_capacity * sizeof(TgItem)));
   TG_CUDA(cudaMalloc(&env->queue_count, 64));
   TG_CUDA(cudaMalloc(&env->counters_dev, sizeof(TgCounters)));

@@ -130,6 +130,10 @@ class CollisionWorld:
         k = ("definite_collisions", "narrow_items", "overflow_inline", "launches")
         return dict(zip(k, [int(v) for v in out]))
 
+    def set_queue_limit(self, items: int) -> None:
+        """Test hook: shrink the ambiguous queue (0 = whole queue) to exercise the inline overflow path."""
+        N.check(self._lib.tg_env_set_queue_limit(self._h, int(items)), "tg_env_set_queue_limit")
+
     def set_timing(self, on: bool) -> None:
         N.check(self._lib.tg_env_set_timing(self._h, int(bool(on))), "tg_env_set_timing")
 

@@ -70,6 +70,9 @@ def traffic_from_profile(cfg_per_launch, vpm):
             "source": t["source"]}
 
 
+_REAL_STDOUT = 1
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons through NVML while the timed region runs."""
 
@@ -132,7 +135,18 @@ def cpu_arm(args, cloud, n_steps, n_warm):
     }
 
 
+def emit(line: dict) -> None:
+    """The ONE JSON line of the contract, written to the process's original stdout."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    # Libraries chat on stdout (NCCL prints "NCCL version ..." when its communicator comes up): everything except the
+    # JSON line goes to stderr.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -158,7 +172,7 @@ def main():
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }
-        print(json.dumps(line))
+        emit(line)
         return
 
     import torch
@@ -312,7 +326,7 @@ def main():
     if world == 1 and not args.no_cpu:
         r = cpu_arm(args, cloud, 1, 1)
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 

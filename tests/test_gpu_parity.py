@@ -321,6 +321,44 @@ def test_edge_properties(room):
     assert not (ev & ~end_ok).any()
 
 
+def test_full_size_chunk_independence(room):
+    """BASELINE-size batches cross the library's launch boundaries (2^17 edges, 32 Mi configurations per launch pair):
+    the verdict of a unit must not depend on where in the batch it sits.  Size-independent property: a permuted batch
+    gives the permuted verdicts, and a slice re-checked on its own gives the same bytes."""
+    cloud, w, cc = room
+    n_e = 300_000                                                      # 3 edge launches
+    a0, b0, a1, b1 = synth.random_edges(n_e, seed=61, rrt_like=True)
+    ev, nchk = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1), count=True)
+    ev = ev.cpu().numpy()
+    perm = np.random.default_rng(62).permutation(n_e)
+    ev_p, nchk_p = w.check_edges(_cuda(a0[perm]), _cuda(b0[perm]), _cuda(a1[perm]), _cuda(b1[perm]), count=True)
+    assert np.array_equal(ev_p.cpu().numpy(), ev[perm]) and int(nchk.item()) == int(nchk_p.item())
+    sl = slice(131_000, 133_000)                                       # straddles the first launch boundary
+    ev_s = w.check_edges(_cuda(a0[sl]), _cuda(b0[sl]), _cuda(a1[sl]), _cuda(b1[sl])).cpu().numpy()
+    assert np.array_equal(ev_s, ev[sl])
+    cl, _ = cc.edge_clearance(a0[sl], b0[sl], a1[sl], b1[sl])
+    _assert_verdicts(ev_s, cl, "edges across a launch boundary")
+    # configurations: 40 Mi = two launch pairs (32 Mi + 8 Mi); generated on the device, checked by slices + the C oracle
+    B = 40 * (1 << 20)
+    g = torch.Generator(device="cuda")
+    g.manual_seed(63)
+    lo = torch.tensor(synth.JOINT_LOWER, dtype=torch.float32, device="cuda")
+    hi = torch.tensor(synth.JOINT_UPPER, dtype=torch.float32, device="cuda")
+    arm = torch.rand(B, 8, generator=g, device="cuda") * (hi - lo) + lo
+    blo = torch.tensor([-3.5, -2.5, -np.pi], dtype=torch.float32, device="cuda")
+    bhi = torch.tensor([3.5, 2.5, np.pi], dtype=torch.float32, device="cuda")
+    base = torch.rand(B, 3, generator=g, device="cuda") * (bhi - blo) + blo
+    valid = w.check_configs(arm, base)
+    assert w.counters()["overflow_inline"] == 0
+    for start in (0, (32 << 20) - 1000, B - 2000):                     # head, the launch boundary, tail
+        s2 = slice(start, start + 2000)
+        again = w.check_configs(arm[s2].contiguous(), base[s2].contiguous())
+        assert torch.equal(again, valid[s2])
+        cl = cc.clearance(arm[s2].cpu().numpy(), base[s2].cpu().numpy())
+        _assert_verdicts(valid[s2].cpu().numpy(), cl, "configs at %d" % start)
+    assert 0.05 < valid.float().mean().item() < 0.6
+
+
 # ------------------------------------------------------------------ self-filter
 def test_filter_points_bit_exact_vs_reference_golden(golden):
     g = golden("self_filter.npz")

@@ -250,19 +250,20 @@ k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __rest
 }
 
 // ---- K4 v3: streaming fast path (full-resolution frames, mask only) --------------------------------
-// Persistent blocks, two per SM.  A block owns a contiguous range of "chunks" (R full image rows of one
-// state = one contiguous piece of the depth array) and pulls them through a 4-stage shared-memory ring
-// with 1-D bulk async copies (cp.async.bulk + mbarrier complete_tx, L2 evict-first): one thread keeps
-// up to 4 x 20 KB per block = 160 KB per SM in flight, independent of register pressure and occupancy,
-// which is what an HBM-bound stream needs (6.5 TB/s x ~1 us latency = 44 KB per SM at the very least).
-// While a chunk is in flight the warps cull the robot's spheres against the chunk's 32-pixel-wide
-// tiles exactly like k_self_filter_tiles (sphere depth interval x projected box, conservative); the
-// 128-bit candidate mask of each tile goes to shared memory.  Consumers read 4 pixels per thread from
-// the ring (conflict-free LDS.128); a pixel costs three compares unless its tile has candidates AND its
-// depth falls into a candidate's depth interval — then it is transformed and tested with the generic
-// kernel's arithmetic (same rounding, same verdict), so the mask stays byte-identical.
+// Persistent blocks, four per SM, each one producer warp + four consumer warps.  A block owns every gridDim-th
+// "chunk" (R = 8 full image rows of one state = one contiguous 20 KB piece of the depth array) and pulls them
+// through a 2-slot shared-memory ring with 1-D bulk async copies (cp.async.bulk + mbarrier complete_tx, L2
+// evict-first): 8 x 20 KB per SM in flight, independent of register pressure and occupancy, which is what an
+// HBM-bound stream needs (6.5 TB/s x ~1 us latency = 44 KB per SM at the very least).  While a chunk is in flight
+// the producer warp culls the robot's spheres against the chunk's rows (band list); consumers read 2 x 4 pixels
+// per lane from the ring (conflict-free LDS.128); a pixel costs one integer compare unless its 32 x 8 tile has
+// candidates in the band list AND in its depth range — then it is classified in the camera frame, and only pixels
+// in a 4 mm shell around a sphere surface are transformed and tested with the generic kernel's arithmetic (same
+// rounding, same verdict), so the mask stays byte-identical.  Measured A/B (C3, ms): 2 blocks x 8 consumers, 32 x 4
+// tiles, 4 slots 0.389; 32 x 8 tiles with 10 consumers 0.42, 16-row chunks 0.35, 3 x 5 consumers 0.346, 4 x 4
+// consumers with 2 slots 0.334 (more producers, more blocks to hide the fixed-latency dependencies).
 #ifndef TGS_STAGES
-#define TGS_STAGES 4
+#define TGS_STAGES 2
 #endif
 #ifndef TGS_STAGE_BYTES
 #define TGS_STAGE_BYTES 20480
@@ -298,10 +299,13 @@ __device__ __forceinline__ void tg_mbar_wait(uint32_t bar_addr, uint32_t parity,
 }
 
 #ifndef TGS_CONSUMERS
-#define TGS_CONSUMERS 8                         // consumer warps; warp TGS_CONSUMERS is the producer
+#define TGS_CONSUMERS 4                         // consumer warps; warp TGS_CONSUMERS is the producer
 #endif
 #ifndef TGS_BLOCKS_PER_SM
-#define TGS_BLOCKS_PER_SM 2
+#define TGS_BLOCKS_PER_SM 4
+#endif
+#ifndef TGS_NF4
+#define TGS_NF4 2                               // float4 per lane and tile: tiles are 32 x 4 or 32 x 8 pixels
 #endif
 #define TGS_THREADS ((TGS_CONSUMERS + 1) * 32)
 #define TGS_STATE_BYTES ((int)((sizeof(TgFilterState) + 127) / 128 * 128))
@@ -430,29 +434,42 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
     tg_mbar_wait(full0 + 8 * slot, (uint32_t)round & 1u, 40);
     const int4 meta = *reinterpret_cast<const int4*>(base + TGS_STAGE_BYTES + TGS_STATE_BYTES + TGS_LIST_BYTES);
     const int cnt = meta.x, u_lo = meta.y, u_hi = meta.z, nq = (cnt + 31) >> 5;
-    // one warp = one tile of 32 x 4 pixels; lane = 4 consecutive pixels (one float4) of row 4 ty + lr.  Compact tiles
-    // keep the candidate lists short (128 x 1 strips were 25 % slower).
-    const int nty = (rows + 3) >> 2;
+    // one warp = one tile of 32 x (4 TGS_NF4) pixels; lane = TGS_NF4 float4 (4 consecutive pixels each) in rows
+    // TH ty + lr (+ 4).  Compact tiles keep the candidate lists short (128 x 1 strips were 25 % slower).
+    constexpr int NF = TGS_NF4, TH = 4 * NF, NP = 4 * NF;
+    const int nty = (rows + TH - 1) / TH;
     int tx = warp, ty = 0;
     while (tx >= ntx) { tx -= ntx; ++ty; }
     while (ty < nty) {
-      const int c4 = 8 * tx + lc, rl = 4 * ty + lr;
+      const int c4 = 8 * tx + lc, rl = TH * ty + lr;
       const int f = rl * w4 + c4;  // float4 index in the chunk = uint32 index in the chunk's mask rows
-      const bool have = c4 < w4 && rl < rows;
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (have) v = buf[f];
-      const float z[4] = {v.x, v.y, v.z, v.w};
+      bool have[NF];
+      float z[NP];
+      uint32_t okb[NF];  // mask bytes of the lane's pixels
+#pragma unroll
+      for (int h = 0; h < NF; ++h) {
+        have[h] = c4 < w4 && rl + 4 * h < rows;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (have[h]) v = buf[f + 4 * h * w4];
+        z[4 * h] = v.x; z[4 * h + 1] = v.y; z[4 * h + 2] = v.z; z[4 * h + 3] = v.w;
+      }
       // z in [lo, hi] with lo > 0: positive floats order like their bit patterns, everything else (negative, -0, NaN)
       // wraps to a huge unsigned difference -> one subtract + one unsigned compare per pixel
-      uint32_t okb = 0;  // mask bytes of the 4 pixels
 #pragma unroll
-      for (int k = 0; k < 4; ++k) okb |= (__float_as_uint(z[k]) - ok_lo <= ok_span ? 1u : 0u) << (8 * k);
+      for (int h = 0; h < NF; ++h) {
+        okb[h] = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) okb[h] |= (__float_as_uint(z[4 * h + k]) - ok_lo <= ok_span ? 1u : 0u) << (8 * k);
+      }
       if (cnt != 0 && 32 * tx + 31 >= u_lo && 32 * tx <= u_hi) {  // warp-uniform: a band sphere reaches these columns
-        uint32_t ok = (okb & 1u) | (okb >> 7 & 2u) | (okb >> 14 & 4u) | (okb >> 21 & 8u);
+        uint32_t ok = 0;
+#pragma unroll
+        for (int h = 0; h < NF; ++h)
+          ok |= ((okb[h] & 1u) | (okb[h] >> 7 & 2u) | (okb[h] >> 14 & 4u) | (okb[h] >> 21 & 8u)) << (4 * h);
         // depth range of the tile's valid pixels: positive floats order like their bit patterns -> one REDUX each
         uint32_t lo_b = 0x7f800000u, hi_b = 0u;
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
+        for (int k = 0; k < NP; ++k)
           if (ok >> k & 1u) { lo_b = min(lo_b, __float_as_uint(z[k])); hi_b = max(hi_b, __float_as_uint(z[k])); }
         const float zlo = __uint_as_float(__reduce_min_sync(0xffffffffu, lo_b));
         const float zhi = __uint_as_float(__reduce_max_sync(0xffffffffu, hi_b));
@@ -460,9 +477,9 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
         if (zlo <= zhi) {
           // candidate spheres: depth interval meets the tile's depth range and, over that depth range, the tile's
           // back-projected box meets the sphere's box (conservative)
-          const int u0 = tx << 5, v0 = row0 + 4 * ty;
+          const int u0 = tx << 5, v0 = row0 + TH * ty;
           const float a0 = ((float)u0 - 0.5f - cxf) * ifx, a1 = ((float)(u0 + 32) - 0.5f - cxf) * ifx;
-          const float b0 = ((float)v0 - 0.5f - cyf) * ify, b1 = ((float)(v0 + 4) - 0.5f - cyf) * ify;
+          const float b0 = ((float)v0 - 0.5f - cyf) * ify, b1 = ((float)(v0 + TH) - 0.5f - cyf) * ify;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             if (q < nq) {  // warp-uniform
@@ -481,10 +498,11 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
           }
         }
         if ((m[0] | m[1] | m[2] | m[3]) != 0u) {  // warp-uniform: the robot may be visible in this tile
-          const float ay = ((float)(row0 + rl) - cyf) * ify;
-          float ax[4];
+          float ax[4], ay[NF];
 #pragma unroll
           for (int k = 0; k < 4; ++k) ax[k] = ((float)(4 * c4 + k) - cxf) * ifx;
+#pragma unroll
+          for (int h = 0; h < NF; ++h) ay[h] = ((float)(row0 + rl + 4 * h) - cyf) * ify;
           uint32_t inside = 0, shell = 0;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
@@ -493,8 +511,8 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
               const float4 e = list[32 * q + __ffs(bits) - 1];
               bits &= bits - 1;
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                const float dx = fmaf(z[k], ax[k], -e.x), dy = fmaf(z[k], ay, -e.y), dz = z[k] - e.z;
+              for (int k = 0; k < NP; ++k) {
+                const float dx = fmaf(z[k], ax[k & 3], -e.x), dy = fmaf(z[k], ay[k >> 2], -e.y), dz = z[k] - e.z;
                 const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
                 inside |= (d2 < rin2 ? 1u : 0u) << k;
                 shell |= (d2 < rout2 ? 1u : 0u) << k;
@@ -506,8 +524,11 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
           while (need) {  // rare (2 mm shells): exact transform + exact test, same arithmetic as the generic kernel
             const int k = __ffs(need) - 1;
             need &= need - 1;
-            const int uu = 4 * c4 + k, vv = row0 + rl;
-            float zz = k == 0 ? z[0] : k == 1 ? z[1] : k == 2 ? z[2] : z[3];
+            const int uu = 4 * c4 + (k & 3), vv = row0 + rl + (k & ~3);
+            float zz = 0.f;
+#pragma unroll
+            for (int kk = 0; kk < NP; ++kk)
+              if (kk == k) zz = z[kk];  // register select: keeps z[] out of local memory
             if (isinf(zz)) zz = 3.4028234663852886e38f;  // np.nan_to_num (only reachable with zmax = inf)
             const float xc = (float)((((double)(float)uu - p.cx) * (double)zz) / p.fx);
             const float yc = (float)((((double)(float)vv - p.cy) * (double)zz) / p.fy);
@@ -528,10 +549,14 @@ k_self_filter_stream(const float* __restrict__ depth, const TgFilterState* __res
             }
             if (in) ok &= ~(1u << k);
           }
+#pragma unroll
+          for (int h = 0; h < NF; ++h)  // bit k of the nibble lands on bit 8k (k + 7k) of the product, no carries
+            okb[h] = ((ok >> (4 * h) & 0xFu) * 0x00204081u) & 0x01010101u;
         }
-        okb = (ok * 0x00204081u) & 0x01010101u;  // bit k of ok lands on bit 8k (k + 7k) of the product, no carries
       }
-      if (have) __stcs(mrow + f, okb);
+#pragma unroll
+      for (int h = 0; h < NF; ++h)
+        if (have[h]) __stcs(mrow + f + 4 * h * w4, okb[h]);
       tx += TGS_CONSUMERS;
       while (tx >= ntx) { tx -= ntx; ++ty; }
     }

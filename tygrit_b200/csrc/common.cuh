@@ -20,6 +20,8 @@
 #define TG_MAGIC_BITS 0x4B000000u  // bit pattern of 2^23
 #define TG_HEADER_BYTES 4096
 #define TG_CLEARANCE_CAP 0.25f
+#define TG_HOST_MAX_CHUNKS 4096
+#define TG_HOST_SMALL 16384  // host batches up to this size go through one packed H2D copy and one D2H copy
 
 struct TgGrid {
   // distance-bound grid
@@ -158,6 +160,10 @@ struct tg_env {
   float* dev_clear[2];
   float* pin_clear[2];
   int64_t chunk;
+  int64_t* dev_checks;  // per-chunk sample counters of the host edge pipeline (TG_HOST_MAX_CHUNKS entries)
+  int64_t* pin_checks;
+  float* pin_small;      // pinned staging of the small-batch host path (one H2D, one D2H per call)
+  uint8_t* pin_small_out;
   int sm_count;
   int occ_configs, occ_resolve;  // resident blocks per SM of the persistent query kernels
 };

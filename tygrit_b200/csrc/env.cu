@@ -452,6 +452,10 @@ extern "C" int tg_env_destroy(tg_env* env) {
     cudaFreeHost(env->pin_in[i]); cudaFreeHost(env->pin_out[i]); cudaFreeHost(env->pin_clear[i]);
     cudaFree(env->dev_in[i]); cudaFree(env->dev_out[i]); cudaFree(env->dev_clear[i]);
   }
+  cudaFree(env->dev_checks);
+  cudaFreeHost(env->pin_checks);
+  cudaFreeHost(env->pin_small);
+  cudaFreeHost(env->pin_small_out);
   if (env->timing_events) {
     for (cudaEvent_t e : *env->timing_events) cudaEventDestroy(e);
     delete env->timing_events;

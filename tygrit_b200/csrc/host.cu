@@ -5,6 +5,8 @@
 // memory; it is cut into chunks that alternate between two streams so the H2D copy of chunk i+1,
 // the kernels of chunk i and the D2H copy of chunk i-1 overlap.  With pinned host buffers the
 // path is PCIe-bound (44 B in + 1 B out per configuration).
+#include <string.h>
+
 #include "common.cuh"
 
 static int tg_host_prepare(tg_env* env) {
@@ -17,6 +19,10 @@ static int tg_host_prepare(tg_env* env) {
     TG_CUDA(cudaMalloc(&env->dev_out[i], (size_t)env->chunk + 64));
     TG_CUDA(cudaMalloc(&env->dev_clear[i], sizeof(float) * (size_t)env->chunk));
   }
+  TG_CUDA(cudaMalloc(&env->dev_checks, sizeof(int64_t) * TG_HOST_MAX_CHUNKS));
+  TG_CUDA(cudaMallocHost(&env->pin_checks, sizeof(int64_t) * TG_HOST_MAX_CHUNKS));
+  TG_CUDA(cudaMallocHost(&env->pin_small, sizeof(float) * 22 * TG_HOST_SMALL));
+  TG_CUDA(cudaMallocHost(&env->pin_small_out, 5 * TG_HOST_SMALL + 64));
   return TG_OK;
 }
 
@@ -28,6 +34,24 @@ extern "C" int tg_check_configs_host(tg_env* env, const float* arm, const float*
   int rc = tg_host_prepare(env);
   if (rc) return rc;
   TG_CUDA(cudaDeviceSynchronize());  // the world may have been built on another stream
+  if (B <= TG_HOST_SMALL) {
+    // small batch (the one-configuration-at-a-time calls of the reference surface land here): pack into pinned staging,
+    // ONE H2D copy, the kernels, ONE D2H copy — a pageable-memory cudaMemcpyAsync costs more than the kernels
+    cudaStream_t st = env->streams[0];
+    float* d_arm = env->dev_in[0];
+    float* d_base = d_arm + 8 * B;
+    memcpy(env->pin_small, arm, sizeof(float) * 8 * B);
+    memcpy(env->pin_small + 8 * B, base, sizeof(float) * 3 * B);
+    TG_CUDA(cudaMemcpyAsync(d_arm, env->pin_small, sizeof(float) * 11 * B, cudaMemcpyHostToDevice, st));
+    rc = tg_check_configs_slot(env, d_arm, d_base, B, env->dev_out[0], clearance ? env->dev_clear[0] : nullptr, st, 0);
+    if (rc) return rc;
+    TG_CUDA(cudaMemcpyAsync(env->pin_small_out, env->dev_out[0], (size_t)B, cudaMemcpyDeviceToHost, st));
+    if (clearance) TG_CUDA(cudaMemcpyAsync(env->pin_small, env->dev_clear[0], sizeof(float) * B, cudaMemcpyDeviceToHost, st));
+    TG_CUDA(cudaStreamSynchronize(st));
+    memcpy(valid, env->pin_small_out, (size_t)B);
+    if (clearance) memcpy(clearance, env->pin_small, sizeof(float) * B);
+    return TG_OK;
+  }
   const int64_t chunk = env->chunk;
   int c = 0;
   for (int64_t off = 0; off < B; off += chunk, ++c) {
@@ -58,12 +82,38 @@ extern "C" int tg_check_edges_host(tg_env* env, const float* arm0, const float* 
   int rc = tg_host_prepare(env);
   if (rc) return rc;
   TG_CUDA(cudaDeviceSynchronize());
+  if (E <= TG_HOST_SMALL) {  // small batch: one packed H2D copy, one D2H copy (verdict bytes + the sample counter)
+    cudaStream_t st = env->streams[0];
+    float* d_a0 = env->dev_in[0];
+    float* d_a1 = d_a0 + 8 * E;
+    float* d_b0 = d_a1 + 8 * E;
+    float* d_b1 = d_b0 + 3 * E;
+    memcpy(env->pin_small, arm0, sizeof(float) * 8 * E);
+    memcpy(env->pin_small + 8 * E, arm1, sizeof(float) * 8 * E);
+    memcpy(env->pin_small + 16 * E, base0, sizeof(float) * 3 * E);
+    memcpy(env->pin_small + 19 * E, base1, sizeof(float) * 3 * E);
+    TG_CUDA(cudaMemcpyAsync(d_a0, env->pin_small, sizeof(float) * 22 * E, cudaMemcpyHostToDevice, st));
+    const size_t cnt_off = ((size_t)E + 7) & ~(size_t)7;
+    int64_t* d_cnt = reinterpret_cast<int64_t*>(env->dev_out[0] + cnt_off);
+    rc = tg_check_edges_slot(env, d_a0, d_b0, d_a1, d_b1, E, rake, resolution, env->dev_out[0], d_cnt, st, 0);
+    if (rc) return rc;
+    TG_CUDA(cudaMemcpyAsync(env->pin_small_out, env->dev_out[0], cnt_off + sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    TG_CUDA(cudaStreamSynchronize(st));
+    memcpy(valid, env->pin_small_out, (size_t)E);
+    if (n_checks) memcpy(n_checks, env->pin_small_out + cnt_off, sizeof(int64_t));
+    return TG_OK;
+  }
   const int64_t chunk = env->chunk / 4;
   const int64_t n_chunks = (E + chunk - 1) / chunk;
-  int64_t* d_checks = nullptr;   // one counter per chunk, summed on the host at the end
-  int64_t* h_checks = nullptr;
-  TG_CUDA(cudaMalloc(&d_checks, sizeof(int64_t) * n_chunks));
-  TG_CUDA(cudaMallocHost(&h_checks, sizeof(int64_t) * n_chunks));
+  // one counter per chunk, summed on the host at the end; preallocated (a cudaMalloc + cudaMallocHost pair per call
+  // costs more than a small batch's kernels)
+  const bool own = n_chunks > TG_HOST_MAX_CHUNKS;
+  int64_t* d_checks = env->dev_checks;
+  int64_t* h_checks = env->pin_checks;
+  if (own) {
+    TG_CUDA(cudaMalloc(&d_checks, sizeof(int64_t) * n_chunks));
+    TG_CUDA(cudaMallocHost(&h_checks, sizeof(int64_t) * n_chunks));
+  }
   int c = 0;
   for (int64_t off = 0; off < E; off += chunk, ++c) {
     const int b = c & 1;
@@ -87,8 +137,10 @@ extern "C" int tg_check_edges_host(tg_env* env, const float* arm0, const float* 
   cudaStreamSynchronize(env->streams[1]);
   if (rc == TG_OK && n_checks)
     for (int64_t i = 0; i < n_chunks; ++i) *n_checks += h_checks[i];
-  cudaFree(d_checks);
-  cudaFreeHost(h_checks);
+  if (own) {
+    cudaFree(d_checks);
+    cudaFreeHost(h_checks);
+  }
   if (rc) return rc;
   TG_CUDA(cudaGetLastError());
   return TG_OK;

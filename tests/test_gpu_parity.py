@@ -435,7 +435,7 @@ def test_self_filter_depth_batch_vs_oracle():
     depth = _numpy_depth(states, boxes, H, W, K, 0)
     depth[:, ::7, ::5] = 0.0
     depth[0, 3, 4] = np.nan
-    for stride in (1, 4):
+    for stride in (1, 2, 4):
         mask, world = engine.self_filter_depth(_cuda(depth), K, _cuda(states), 0.08, (0.2, 3.0), stride, want_world=True)
         mask, world = mask.cpu().numpy().astype(bool), world.cpu().numpy()
         n_removed = 0
@@ -453,9 +453,10 @@ def test_self_filter_depth_batch_vs_oracle():
             assert not mask[s][~keep].any()                             # invalid depth is never kept
             n_removed += int((signed < 0).sum())
         assert n_removed > 50                                           # the robot was really in view
-        if stride == 1:   # the tile-culled fast path (mask only) must give the generic kernel's mask, byte for byte
-            fast = engine.self_filter_depth(_cuda(depth), K, _cuda(states), 0.08, (0.2, 3.0), 1).cpu().numpy().astype(bool)
-            assert np.array_equal(fast, mask)
+        # the mask-only paths (streaming kernel at stride 1, camera-frame prefilter otherwise) must give the mask of the
+        # path that also writes the world points, byte for byte
+        fast = engine.self_filter_depth(_cuda(depth), K, _cuda(states), 0.08, (0.2, 3.0), stride).cpu().numpy().astype(bool)
+        assert np.array_equal(fast, mask)
 
 
 @pytest.mark.parametrize("shape", [(480, 640, 24), (100, 164, 24), (480, 640, 96), (37, 2048, 5)])
@@ -478,6 +479,9 @@ def test_self_filter_fast_path_equals_generic_kernel(shape):
     slow, _ = engine.self_filter_depth(depth, K, st, 0.08, (0.2, 3.0), 1, want_world=True)
     fast = engine.self_filter_depth(depth, K, st, 0.08, (0.2, 3.0), 1)
     assert torch.equal(fast, slow)
+    for stride in (2, 4):                                             # strided mask-only path vs the path with world output
+        slow_s, _ = engine.self_filter_depth(depth, K, st, 0.08, (0.2, 3.0), stride, want_world=True)
+        assert torch.equal(engine.self_filter_depth(depth, K, st, 0.08, (0.2, 3.0), stride), slow_s)
     removed = ((depth > 0.2) & (depth < 3.0) & (slow == 0)).float().mean().item()
     assert removed > 1e-3                                             # robot pixels exist in these frames
 

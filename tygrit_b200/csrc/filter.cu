@@ -184,9 +184,10 @@ k_filter_prepare(const float* __restrict__ states, int S, float radius, TgDepthP
 // one thread = PIX consecutive decimated pixels of one state
 template <int PIX>
 __global__ void __launch_bounds__(TGF_BLOCK)
-k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __restrict__ prep, TgDepthParams p,
+k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __restrict__ prep, TgDepthParams p, float radius,
                     uint8_t* __restrict__ mask, float* __restrict__ world) {
   __shared__ TgFilterState st;
+  const float rp = radius + 2e-3f, rout2 = rp * rp, rin = fmaxf(radius - 2e-3f, 0.f), rin2 = rin * rin;
   const int s = blockIdx.y;
   {
     const float* src = reinterpret_cast<const float*>(prep + s);
@@ -195,8 +196,29 @@ k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __rest
   }
   __syncthreads();
   const int npx = p.Hs * p.Ws;
-  const int first = (blockIdx.x * TGF_BLOCK + threadIdx.x) * PIX;
-  if (first >= npx) return;
+  // mask-only calls: the spheres that can meet this block's image rows at all (depth interval x projected y-range,
+  // conservative), compacted into shared memory — the per-pixel loop below walks ~20 of them instead of 111
+  __shared__ float4 s_list[TGM_N_SPHERES];
+  __shared__ int s_cnt;
+  if (threadIdx.x == 0) s_cnt = 0;
+  __syncthreads();
+  if (world == nullptr && threadIdx.x < TGM_N_SPHERES) {
+    const bool whole = (long long)gridDim.x * TGF_BLOCK * PIX < npx;  // the block loops over several row ranges
+    const int p0 = blockIdx.x * TGF_BLOCK * PIX, p1 = min(p0 + TGF_BLOCK * PIX, npx) - 1;
+    const int v0 = whole ? 0 : p0 / p.Ws, v1 = whole ? p.Hs - 1 : p1 / p.Ws;
+    const float b0 = ((float)v0 - 0.5f - (float)p.cy) * (float)(1.0 / p.fy), b1 = ((float)v1 + 0.5f - (float)p.cy) * (float)(1.0 / p.fy);
+    const int j = threadIdx.x;
+    const float X = st.cc[3 * j], Y = st.cc[3 * j + 1], Z = st.cc[3 * j + 2];
+    const float zl = fmaxf(fmaxf(Z - rp, p.zmin - 1e-3f), 0.f), zh = fminf(Z + rp, p.zmax + 1e-3f);
+    if (zl <= zh) {
+      const float ymin = (b0 >= 0.f ? zl : zh) * b0, ymax = (b1 >= 0.f ? zh : zl) * b1;
+      if (ymin <= Y + rp && ymax >= Y - rp) s_list[atomicAdd(&s_cnt, 1)] = make_float4(X, Y, Z, 0.f);
+    }
+  }
+  __syncthreads();
+  const int cnt = s_cnt;
+  // a block walks the frame in steps of gridDim.x * TGF_BLOCK * PIX pixels (one step with the launch shape used today)
+  for (int first = (blockIdx.x * TGF_BLOCK + threadIdx.x) * PIX; first < npx; first += gridDim.x * TGF_BLOCK * PIX) {
   const float* img = depth + (size_t)s * p.H * p.W;
   float d[PIX];
   if (PIX == 4 && p.stride == 1 && (p.W & 3) == 0) {
@@ -222,6 +244,31 @@ k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __rest
     else if (isinf(z)) z = z > 0 ? 3.4028234663852886e38f : -3.4028234663852886e38f;
     bool ok = pix < npx && z > 0.f && z >= p.zmin && z <= p.zmax;
     float wx = 0.f, wy = 0.f, wz = 0.f;
+    if (ok && world == nullptr) {
+      // mask only: settle the pixel in the camera frame where that is safe (see k_self_filter_stream): outside the
+      // robot's image-space box, or farther than r + 2 mm from every sphere -> kept; closer than r - 2 mm to one ->
+      // removed; only the 4 mm shells take the reference-exact path below
+      if ((float)u < st.img_box[0] || (float)u > st.img_box[2] || (float)v < st.img_box[1] || (float)v > st.img_box[3]) {
+        out[k] = 1;
+        continue;
+      }
+      const float xa = ((float)u - (float)p.cx) * (float)(1.0 / p.fx) * z, ya = ((float)v - (float)p.cy) * (float)(1.0 / p.fy) * z;
+      bool in = false, shell = false;
+      for (int s2 = 0; s2 < cnt; ++s2) {
+        const float4 e = s_list[s2];
+        const float dz = z - e.z;
+        if (fabsf(dz) < rp) {
+          const float dx = xa - e.x, dy = ya - e.y;
+          const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+          in |= d2 < rin2;
+          shell |= d2 < rout2;
+        }
+      }
+      if (in || !shell) {
+        out[k] = in ? 0 : 1;
+        continue;
+      }
+    }
     if (ok) {
       // depth.py:41-46 evaluated as numpy 2 does: (f32 index - f64 c) * f32 depth / f64 f, rounded once
       const float xc = (float)((((double)(float)u - p.cx) * (double)z) / p.fx);
@@ -246,6 +293,7 @@ k_self_filter_depth(const float* __restrict__ depth, const TgFilterState* __rest
 #pragma unroll
     for (int k = 0; k < PIX; ++k)
       if (first + k < npx) m[k] = out[k];
+  }
   }
 }
 
@@ -605,8 +653,9 @@ extern "C" int tg_self_filter_depth(const float* depth, int H, int W, int stride
     const int blocks = min(sms * TGS_BLOCKS_PER_SM, total);
     k_self_filter_stream<<<blocks, TGS_THREADS, smem, st>>>(depth, prep, p, radius, mask, R, cpf, total);
   } else {
-    dim3 grid(tg_div_up(npx, TGF_BLOCK * 4), (unsigned)S);
-    k_self_filter_depth<4><<<grid, TGF_BLOCK, 0, st>>>(depth, prep, p, mask, world);
+    const int per_state = tg_div_up(npx, TGF_BLOCK * 4);  // many small blocks: measured faster than fewer looping ones
+    dim3 grid(per_state, (unsigned)S);
+    k_self_filter_depth<4><<<grid, TGF_BLOCK, 0, st>>>(depth, prep, p, radius, mask, world);
   }
   TG_CUDA(cudaGetLastError());
   TG_CUDA(cudaFreeAsync(prep, st));

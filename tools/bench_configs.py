@@ -76,7 +76,7 @@ def c2(args):
         e = [cuda(x) for x in synth.random_edges(100_000, rrt_like=rrt)]
         valid, n = w.check_edges(*e, count=True)
         checks = int(n.item())
-        ms = timed(lambda: w.check_edges(*e), 10)
+        ms = timed(lambda: w.check_edges(*e), 100, warm=100)
         out[name] = {"ms": ms, "edges_per_s": 1e5 / (ms * 1e-3), "config_checks": checks,
                      "config_checks_per_s": checks / (ms * 1e-3), "valid_fraction": float(valid.float().mean().item())}
     return {"config": "C2: 100k random Fetch edges (rake 8, resolution 32) vs 200k-point room cloud", **out}

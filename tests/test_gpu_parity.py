@@ -326,14 +326,14 @@ def test_full_size_chunk_independence(room):
     the verdict of a unit must not depend on where in the batch it sits.  Size-independent property: a permuted batch
     gives the permuted verdicts, and a slice re-checked on its own gives the same bytes."""
     cloud, w, cc = room
-    n_e = 300_000                                                      # 3 edge launches
+    n_e = 1_200_000                                                    # 3 edge launches (2^19 edges each)
     a0, b0, a1, b1 = synth.random_edges(n_e, seed=61, rrt_like=True)
     ev, nchk = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1), count=True)
     ev = ev.cpu().numpy()
     perm = np.random.default_rng(62).permutation(n_e)
     ev_p, nchk_p = w.check_edges(_cuda(a0[perm]), _cuda(b0[perm]), _cuda(a1[perm]), _cuda(b1[perm]), count=True)
     assert np.array_equal(ev_p.cpu().numpy(), ev[perm]) and int(nchk.item()) == int(nchk_p.item())
-    sl = slice(131_000, 133_000)                                       # straddles the first launch boundary
+    sl = slice((1 << 19) - 1000, (1 << 19) + 1000)                     # straddles the first launch boundary
     ev_s = w.check_edges(_cuda(a0[sl]), _cuda(b0[sl]), _cuda(a1[sl]), _cuda(b1[sl])).cpu().numpy()
     assert np.array_equal(ev_s, ev[sl])
     cl, _ = cc.edge_clearance(a0[sl], b0[sl], a1[sl], b1[sl])

@@ -124,6 +124,7 @@ def c5(args):
     checks = int(n.item())
     eb = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     build_ms = 0.0
+    w.counters()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for i in range(steps):
@@ -136,7 +137,9 @@ def c5(args):
             build_ms += eb[0].elapsed_time(eb[1])
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    return {"config": f"C5: {steps} steps x (rebuild 200k-500k-point cloud + {E} edges)", "steps_per_s": steps / dt,
+    cnt = w.counters()
+    return {"narrow_items_per_edge": cnt["narrow_items"] / (steps * E), "overflow_inline": cnt["overflow_inline"],
+            "config": f"C5: {steps} steps x (rebuild 200k-500k-point cloud + {E} edges)", "steps_per_s": steps / dt,
             "ms_per_step": dt / steps * 1e3, "build_us": build_ms / ((steps + 9) // 10) * 1e3, "edges_per_s": steps * E / dt,
             "config_checks_per_s": steps * checks / dt, "valid_fraction": float(valid.float().mean().item())}
 

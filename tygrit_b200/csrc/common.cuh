@@ -44,6 +44,8 @@ struct TgGrid {
   int empty;            // 1 = no cloud geometry
   // device pointers (into the blob)
   const uint8_t* df;
+  unsigned long long df_tex;  // cudaTextureObject_t over a 3-D array copy of df (process-local, set after build / import)
+  float tex_bias[3];          // voxel coordinate -> texel coordinate: 0.5 - m
   const uint32_t* cell_start;
   const float4* pts;
 };
@@ -126,6 +128,9 @@ struct tg_env {
   // blob + scratch
   uint8_t* blob;
   size_t blob_capacity;
+  cudaArray_t df_array;       // block-linear copy of the distance grid, read through the texture path by phase 1
+  cudaTextureObject_t df_tex;
+  int arr_n[3];
   uint8_t* g1;           // EDT pass X output, u8 [nvox]
   uint16_t* g2;          // EDT pass Y output, u16 [nvox]
   uint32_t* cell_count;  // [max_cells + 1]

@@ -384,6 +384,46 @@ static void tg_layout(tg_env* env, TgGrid* g, TgHeader* h) {
   g->pts = (const float4*)(env->blob + h->off_pts);
 }
 
+// Phase 1 reads the distance grid through the texture path: a 3-D cudaArray is stored block-linear, so the spheres of
+// one link (a few cm apart in all three directions) tend to share 32-byte sectors, which a row-major grid only
+// offers along x; the unit also does the index arithmetic and the clamp.  The array is a copy of the blob's linear
+// grid (which stays the thing that is exported / broadcast), refreshed after every build or import.
+static int tg_env_refresh_texture(tg_env* env, cudaStream_t st) {
+  TgGrid& g = env->grid;
+  g.df_tex = 0;
+  if (g.empty) return TG_OK;
+  if (env->df_array == nullptr || env->arr_n[0] != g.nx || env->arr_n[1] != g.ny || env->arr_n[2] != g.nz) {
+    if (env->df_tex) cudaDestroyTextureObject(env->df_tex);
+    if (env->df_array) cudaFreeArray(env->df_array);
+    env->df_tex = 0;
+    env->df_array = nullptr;
+    cudaChannelFormatDesc cd = cudaCreateChannelDesc<unsigned char>();
+    TG_CUDA(cudaMalloc3DArray(&env->df_array, &cd, make_cudaExtent((size_t)g.nx, (size_t)g.ny, (size_t)g.nz)));
+    cudaResourceDesc rd;
+    memset(&rd, 0, sizeof(rd));
+    rd.resType = cudaResourceTypeArray;
+    rd.res.array.array = env->df_array;
+    cudaTextureDesc td;
+    memset(&td, 0, sizeof(td));
+    td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+    td.filterMode = cudaFilterModePoint;
+    td.readMode = cudaReadModeElementType;
+    td.normalizedCoords = 0;
+    TG_CUDA(cudaCreateTextureObject(&env->df_tex, &rd, &td, nullptr));
+    env->arr_n[0] = g.nx; env->arr_n[1] = g.ny; env->arr_n[2] = g.nz;
+  }
+  cudaMemcpy3DParms cp;
+  memset(&cp, 0, sizeof(cp));
+  cp.srcPtr = make_cudaPitchedPtr((void*)g.df, (size_t)g.nx, (size_t)g.nx, (size_t)g.ny);
+  cp.dstArray = env->df_array;
+  cp.extent = make_cudaExtent((size_t)g.nx, (size_t)g.ny, (size_t)g.nz);
+  cp.kind = cudaMemcpyDeviceToDevice;
+  TG_CUDA(cudaMemcpy3DAsync(&cp, st));
+  g.df_tex = (unsigned long long)env->df_tex;
+  for (int a = 0; a < 3; ++a) g.tex_bias[a] = 0.5f - (TG_MAGIC - g.bias[a]);  // bias = 2^23 - m
+  return TG_OK;
+}
+
 extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float voxels_per_metre, float point_radius,
                              int64_t max_voxels) {
   TG_CHECK_ARG(out != nullptr, "tg_env_create: out is NULL");
@@ -452,6 +492,8 @@ extern "C" int tg_env_destroy(tg_env* env) {
     cudaFreeHost(env->pin_in[i]); cudaFreeHost(env->pin_out[i]); cudaFreeHost(env->pin_clear[i]);
     cudaFree(env->dev_in[i]); cudaFree(env->dev_out[i]); cudaFree(env->dev_clear[i]);
   }
+  if (env->df_tex) cudaDestroyTextureObject(env->df_tex);
+  if (env->df_array) cudaFreeArray(env->df_array);
   cudaFree(env->dev_checks);
   cudaFreeHost(env->pin_checks);
   cudaFreeHost(env->pin_small);
@@ -581,7 +623,7 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   h->grid = g;
   h->thr = env->thr;
   TG_CUDA(cudaMemcpyAsync(env->blob, h, sizeof(TgHeader), cudaMemcpyHostToDevice, st));
-  return TG_OK;
+  return tg_env_refresh_texture(env, st);
 }
 
 extern "C" int tg_env_build_host(tg_env* env, const float* xyz, int64_t n, void* stream_) {
@@ -660,7 +702,7 @@ extern "C" int tg_env_import(tg_env* env, const void* blob, size_t bytes, void* 
   env->grid = g;
   env->thr = h->thr;
   env->r_pt = g.r_pt;
-  return TG_OK;
+  return tg_env_refresh_texture(env, st);
 }
 
 extern "C" int tg_env_set_obstacles(tg_env* env, const float* xyzr, int n, void* stream_) {

@@ -22,6 +22,11 @@
 // one, which is equivalent: every boundary voxel is at least W voxels from the cloud (tg_plan_grids pads
 // the box by W + 3), so both read "free".
 __device__ __forceinline__ int tg_probe(const TgGrid& g, float gx, float gy, float gz) {
+#ifndef TG_LINEAR_PROBE
+  // texture path: point sampling floors (g - m + 0.5) = the nearest voxel, clamp addressing keeps probes outside the
+  // grid on a boundary voxel (which reads "free": the box is padded by W + 3 voxels), block-linear array layout
+  return (int)tex3D<unsigned char>((cudaTextureObject_t)g.df_tex, gx + g.tex_bias[0], gy + g.tex_bias[1], gz + g.tex_bias[2]);
+#endif
   const unsigned ux = __viaddmin_u32(__float_as_uint(gx + g.bias[0]), 0u - TG_MAGIC_BITS, (unsigned)(g.nx - 1));
   const unsigned uy = __viaddmin_u32(__float_as_uint(gy + g.bias[1]), 0u - TG_MAGIC_BITS, (unsigned)(g.ny - 1));
   const unsigned uz = __viaddmin_u32(__float_as_uint(gz + g.bias[2]), 0u - TG_MAGIC_BITS, (unsigned)(g.nz - 1));

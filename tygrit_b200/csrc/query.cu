@@ -165,9 +165,16 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
 // warp per sphere: tg_warp_sphere_hits.  A hit marks the item done, so its remaining spheres are
 // skipped.  Items whose sphere count exceeds the list are handled in further passes.
 // ------------------------------------------------------------------------------------------------
-#define TGR_BLOCK 128   // threads per block
-#define TGR_ITEMS 64    // queue items per batch: small batches keep the serial sphere chain per warp short
-#define TGR_CAP 1024    // sphere-list slots per pass
+#ifndef TGR_BLOCK
+#define TGR_BLOCK 96    // threads per block (64 / 96 / 128 threads: 1.417 / 1.408 / 1.462 ms per 32 Mi configurations)
+#endif
+#define TGR_ITEMS (TGR_BLOCK / 2)  // queue items per batch (two threads per item): small batches keep the serial sphere chain per warp short
+#ifndef TGR_CAP
+#define TGR_CAP 768     // sphere-list slots per pass
+#endif
+#ifndef TGR_MINB
+#define TGR_MINB 10
+#endif
 #define TGR_ROUNDS 1    // best-first rounds before the rest of the list is walked in order
 
 __device__ __forceinline__ void tg_emit_frame(const TgFrame& F, const TgBase& b, float r_pt, uint32_t bits, int k_base,
@@ -195,7 +202,7 @@ __device__ __forceinline__ uint32_t tg_mask_range(const uint32_t* mask, int k0, 
   return n >= 32 ? r : (r & ((1u << n) - 1u));
 }
 
-__global__ void __launch_bounds__(TGR_BLOCK, 8) k_resolve(const TgGrid g, TgQueue qu, uint8_t* __restrict__ valid, TgCounters* ctr) {
+__global__ void __launch_bounds__(TGR_BLOCK, TGR_MINB) k_resolve(const TgGrid g, TgQueue qu, uint8_t* __restrict__ valid, TgCounters* ctr) {
   __shared__ float4 s_sph[TGR_CAP];
   __shared__ uint16_t s_own[TGR_CAP];
   __shared__ uint32_t s_key[TGR_CAP];

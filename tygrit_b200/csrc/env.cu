@@ -221,26 +221,38 @@ __device__ __forceinline__ unsigned tge_row_dist2(const uint32_t* __restrict__ r
   return d <= W ? (unsigned)(d * d) : TGE_SENT;
 }
 
-__device__ __forceinline__ unsigned tge_taps(const uint32_t* __restrict__ col /* tile + r*32 + lane */, int W) {
-  unsigned best = col[0];
-#pragma unroll 4
-  for (int k = 1; k <= W; ++k) {
-    const unsigned k2 = (unsigned)(k * k) * 0x10001u;
-    best = __viaddmin_u16x2(col[-32 * k], k2, best);
-    best = __viaddmin_u16x2(col[32 * k], k2, best);
+// Register-blocked taps: one thread produces TGE_T consecutive outputs along the pass axis from TGE_T + 2 WB loaded
+// rows (one LDS per ~10 taps instead of one per tap: the passes were shared-memory-bandwidth bound).  WB >= W is the
+// window rounded up to a multiple of 4 so that the tap offsets and k^2 are compile-time constants with 7
+// instantiations; the extra taps only add candidates > W^2, which the final quantisation maps to 255 like "nothing
+// within W", so the codes are unchanged (bit-exact test against scipy's EDT).
+#define TGE_T 12
+template <int WB>
+__device__ __forceinline__ void tge_taps_blocked(const uint32_t* __restrict__ col /* tile + r0 * 32 + lane */, unsigned (&best)[TGE_T]) {
+#pragma unroll
+  for (int t = 0; t < TGE_T; ++t) best[t] = TGE_SENT2;
+#pragma unroll
+  for (int j = -WB; j < TGE_T + WB; ++j) {
+    const unsigned v = col[32 * j];
+#pragma unroll
+    for (int t = 0; t < TGE_T; ++t) {
+      const int k = j - t;
+      if (k >= -WB && k <= WB) best[t] = __viaddmin_u16x2(v, (unsigned)(k * k) * 0x10001u, best[t]);
+    }
   }
-  return __vminu2(best, TGE_SENT2);
+#pragma unroll
+  for (int t = 0; t < TGE_T; ++t) best[t] = __vminu2(best[t], TGE_SENT2);
 }
 
 // passes X + Y.  grid (ceil(nx/64), ceil(ny/TGE_SEG), nz); g2 is u16 [nz][ny][nxp], nxp even.
+template <int WB>
 __global__ void __launch_bounds__(TGE_THREADS)
 k_edt_xy(const uint32_t* __restrict__ bits, uint32_t* __restrict__ g2w, int nx, int nxp, int nwx, int ny, int W) {
-  extern __shared__ uint32_t tile[];  // [TGE_SEG + 2W][32] packed pairs
+  extern __shared__ uint32_t tile[];  // [TGE_SEG + 2 WB][32] packed pairs
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int x = blockIdx.x * 64 + 2 * lane, y0 = blockIdx.y * TGE_SEG, z = blockIdx.z;
-  const int rows = min(TGE_SEG, ny - y0) + 2 * W;
-  for (int r = warp; r < rows; r += TGE_THREADS / 32) {
-    const int y = y0 - W + r;
+  for (int r = warp; r < TGE_SEG + 2 * WB; r += TGE_THREADS / 32) {
+    const int y = y0 - WB + r;
     unsigned v = TGE_SENT2;
     if (y >= 0 && y < ny && x < nx) {
       const uint32_t* row = bits + ((size_t)z * ny + y) * nwx;
@@ -252,39 +264,61 @@ k_edt_xy(const uint32_t* __restrict__ bits, uint32_t* __restrict__ g2w, int nx, 
   }
   __syncthreads();
   if (x >= nxp) return;
-  for (int r = W + warp; r < rows - W; r += TGE_THREADS / 32) {
-    const int y = y0 - W + r;
-    g2w[(((size_t)z * ny + y) * nxp + x) >> 1] = tge_taps(tile + r * 32 + lane, W);
+  for (int r0 = TGE_T * warp; r0 < TGE_SEG; r0 += TGE_T * (TGE_THREADS / 32)) {
+    if (y0 + r0 >= ny) break;
+    unsigned best[TGE_T];
+    tge_taps_blocked<WB>(tile + (WB + r0) * 32 + lane, best);
+#pragma unroll
+    for (int t = 0; t < TGE_T; ++t) {
+      const int y = y0 + r0 + t;
+      if (y < ny) g2w[(((size_t)z * ny + y) * nxp + x) >> 1] = best[t];
+    }
   }
 }
 
 // pass Z + quantisation.  grid (ceil(nx/64), ny, ceil(nz/TGE_SEG)).
+template <int WB>
 __global__ void __launch_bounds__(TGE_THREADS)
 k_edt_z(const uint32_t* __restrict__ g2w, uint8_t* __restrict__ df, int nx, int nxp, int ny, int nz, int W) {
-  extern __shared__ uint32_t tile[];  // [TGE_SEG + 2W][32] packed pairs, then the code table
+  extern __shared__ uint32_t tile[];  // [TGE_SEG + 2 WB][32] packed pairs
   __shared__ uint8_t lut[1024];       // d2 -> code for d2 < W^2 (W <= 31)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int x = blockIdx.x * 64 + 2 * lane, y = blockIdx.y, z0 = blockIdx.z * TGE_SEG;
-  const int rows = min(TGE_SEG, nz - z0) + 2 * W;
   const float scale = 255.0f / (float)W;
   for (int d2 = threadIdx.x; d2 < 1024; d2 += TGE_THREADS)
     lut[d2] = d2 < W * W ? (uint8_t)min(254, (int)floorf(sqrtf((float)d2) * scale)) : (uint8_t)255;
-  for (int r = warp; r < rows; r += TGE_THREADS / 32) {
-    const int z = z0 - W + r;
+  for (int r = warp; r < TGE_SEG + 2 * WB; r += TGE_THREADS / 32) {
+    const int z = z0 - WB + r;
     unsigned v = TGE_SENT2;
     if (z >= 0 && z < nz && x < nxp) v = __ldg(g2w + ((((size_t)z * ny + y) * nxp + x) >> 1));
     tile[r * 32 + lane] = v;
   }
   __syncthreads();
   if (x >= nx) return;
-  for (int r = W + warp; r < rows - W; r += TGE_THREADS / 32) {
-    const int z = z0 - W + r;
-    const unsigned best = tge_taps(tile + r * 32 + lane, W);
-    const unsigned lo = best & 0xFFFFu, hi = best >> 16;
-    uint8_t* out = df + ((size_t)z * ny + y) * nx + x;
-    out[0] = lo < 1024u ? lut[lo] : (uint8_t)255;
-    if (x + 1 < nx) out[1] = hi < 1024u ? lut[hi] : (uint8_t)255;
+  for (int r0 = TGE_T * warp; r0 < TGE_SEG; r0 += TGE_T * (TGE_THREADS / 32)) {
+    if (z0 + r0 >= nz) break;
+    unsigned best[TGE_T];
+    tge_taps_blocked<WB>(tile + (WB + r0) * 32 + lane, best);
+#pragma unroll
+    for (int t = 0; t < TGE_T; ++t) {
+      const int z = z0 + r0 + t;
+      if (z < nz) {
+        const unsigned lo = best[t] & 0xFFFFu, hi = best[t] >> 16;
+        uint8_t* out = df + ((size_t)z * ny + y) * nx + x;
+        out[0] = lo < 1024u ? lut[lo] : (uint8_t)255;
+        if (x + 1 < nx) out[1] = hi < 1024u ? lut[hi] : (uint8_t)255;
+      }
+    }
   }
+}
+
+template <int WB>
+static void tg_launch_edt(const uint32_t* occ_bits, uint32_t* g2, uint8_t* df, const TgGrid& g, int nxp, int nwx, cudaStream_t st) {
+  const size_t tile_bytes = (size_t)(TGE_SEG + 2 * WB) * 32 * sizeof(uint32_t);
+  k_edt_xy<WB><<<dim3(tg_div_up(nxp, 64), tg_div_up(g.ny, TGE_SEG), g.nz), TGE_THREADS, tile_bytes, st>>>(occ_bits, g2, g.nx, nxp, nwx, g.ny,
+                                                                                                         g.window);
+  k_edt_z<WB><<<dim3(tg_div_up(g.nx, 64), g.ny, tg_div_up(g.nz, TGE_SEG)), TGE_THREADS, tile_bytes, st>>>(g2, df, g.nx, nxp, g.ny, g.nz,
+                                                                                                        g.window);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -610,11 +644,15 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   k_scan_sums<<<1, 1024, 0, st>>>(env->scan_tmp, nb);
   k_scan_apply<<<nb, 256, 0, st>>>(env->cell_count, ncell, env->scan_tmp, cell_start);
   k_scatter<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, env->key, env->rank, cell_start, pts);
-  const size_t tile_bytes = (size_t)(TGE_SEG + 2 * g.window) * 32 * sizeof(uint32_t);
-  k_edt_xy<<<dim3(tg_div_up(nxp, 64), tg_div_up(g.ny, TGE_SEG), g.nz), TGE_THREADS, tile_bytes, st>>>(
-      occ_bits, (uint32_t*)env->g2, g.nx, nxp, nwx, g.ny, g.window);
-  k_edt_z<<<dim3(tg_div_up(g.nx, 64), g.ny, tg_div_up(g.nz, TGE_SEG)), TGE_THREADS, tile_bytes, st>>>(
-      (const uint32_t*)env->g2, df, g.nx, nxp, g.ny, g.nz, g.window);
+  switch ((g.window + 3) / 4) {  // window rounded up to a multiple of 4 (W <= 31)
+    case 0: case 1: case 2: tg_launch_edt<8>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
+    case 3: tg_launch_edt<12>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
+    case 4: tg_launch_edt<16>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
+    case 5: tg_launch_edt<20>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
+    case 6: tg_launch_edt<24>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
+    case 7: tg_launch_edt<28>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
+    default: tg_launch_edt<32>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
+  }
   TG_CUDA(cudaGetLastError());
   env->launches += 7;
 

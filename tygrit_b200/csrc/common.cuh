@@ -56,6 +56,7 @@ struct TgThr {
   int free_ge[TG_N_SPHERES];
   int coll_le[TG_N_SPHERES];
   int bound_ge[16];  // per cull group (fetch_model.cuh TGM_BOUND): enclosing sphere definitely free iff code >= bound_ge
+  int src_ge[TG_N_SPHERES];  // derived bound: sphere definitely free iff the code at its source point (tgm_k_src) >= src_ge
 };
 
 struct TgExtras {  // sphere obstacles + end-effector attachment (rarely used; brute force)

@@ -324,6 +324,9 @@ static void tg_launch_edt(const uint32_t* occ_bits, uint32_t* g2, uint8_t* df, c
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
+#ifndef TG_WINDOW_VOX
+#define TG_WINDOW_VOX 0
+#endif
 static const double kEpsFp = 2e-5;  // metres: fp32 slop of centres / voxel index rounding
 
 static void tg_compute_thresholds(const TgGrid& g, TgThr* thr) {
@@ -342,6 +345,12 @@ static void tg_compute_thresholds(const TgGrid& g, TgThr* thr) {
     const double R = (double)TGM_H_BOUND_RADIUS[b] + (double)g.r_pt;
     thr->bound_ge[b] = (int)floor((R + slack) / q) + 1;  // > 255: the window is too small to ever prove it
   }
+  // code c at the source point => no cloud point within c*q - slack of it; the sphere is inside the ball of radius
+  // sep + r around the source (sep = centre separation in the rigid frame, rounded up in the generator)
+  for (int j = 0; j < TG_N_SPHERES; ++j) {
+    const double R = (double)TGM_H_K_SRCSEP[j] + (double)TGM_H_RADIUS_K[j] + (double)g.r_pt;
+    thr->src_ge[j] = tgm_k_src(j) < 0 ? 256 : (int)floor((R + slack) / q) + 1;
+  }
 }
 
 // choose grid geometry for the cloud box [lo, hi]; returns false if it cannot fit
@@ -351,6 +360,7 @@ static bool tg_plan_grids(tg_env* env, const float lo[3], const float hi[3], TgG
   for (int it = 0; it < 64; ++it) {
     const double slack = sqrt(3.0) / vpm + kEpsFp;
     int W = (int)ceil((r_need + slack + 0.004) * vpm) + 1;
+    if (W < TG_WINDOW_VOX) W = TG_WINDOW_VOX;  // wider than the largest sphere needs: lets the enclosing-sphere probes prove more
     if (W > 31) {  // window too wide for the transform: the grid is finer than useful
       vpm *= 0.9;
       continue;
@@ -607,7 +617,7 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
     memset(&env->thr, 0, sizeof(env->thr));
     TgHeader* h = env->header_host;
     memset(h, 0, sizeof(TgHeader));
-    h->magic = 0x54594752495442ull;
+    h->magic = 0x54594752495443ull;
     h->bytes = TG_HEADER_BYTES;
     h->grid = g;
     TG_CUDA(cudaMemcpyAsync(env->blob, h, sizeof(TgHeader), cudaMemcpyHostToDevice, st));
@@ -621,7 +631,7 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   g.n_points = (int)n;
   TgHeader* h = env->header_host;
   memset(h, 0, sizeof(TgHeader));
-  h->magic = 0x54594752495442ull;
+  h->magic = 0x54594752495443ull;
   tg_layout(env, &g, h);
   if (h->bytes > env->blob_capacity) {
     tg_set_error("tg_env_build: structure needs %zu bytes, capacity %zu", (size_t)h->bytes, env->blob_capacity);
@@ -727,7 +737,7 @@ extern "C" int tg_env_import(tg_env* env, const void* blob, size_t bytes, void* 
   TG_CUDA(cudaMemcpyAsync(env->header_host, env->blob, sizeof(TgHeader), cudaMemcpyDeviceToHost, st));
   TG_CUDA(cudaStreamSynchronize(st));
   TgHeader* h = env->header_host;
-  if (h->magic != 0x54594752495442ull || h->bytes > bytes) {
+  if (h->magic != 0x54594752495443ull || h->bytes > bytes) {
     tg_set_error("tg_env_import: not a tygrit_b200 structure blob");
     return TG_E_ARG;
   }

@@ -33,6 +33,22 @@ __device__ __forceinline__ int tg_probe(const TgGrid& g, float gx, float gy, flo
   return (int)__ldg(g.df + (ux + (unsigned)g.nx * uy + (unsigned)g.nxy * uz));
 }
 
+// Predicated probe: lanes with need == false issue no request and read `skipped`.  Written as predicated PTX inside
+// straight-line code so the texture handle stays in a uniform register (a tex3D under a divergent branch makes the
+// compiler wrap every fetch in a handle-uniformity loop).
+__device__ __forceinline__ int tg_probe_if(const TgGrid& g, bool need, float gx, float gy, float gz, int skipped) {
+#ifndef TG_LINEAR_PROBE
+  unsigned c;
+  asm("{\n\t.reg .pred p;\n\t.reg .u32 t1, t2, t3;\n\tsetp.ne.s32 p, %5, 0;\n\tmov.u32 %0, %6;\n\t"
+      "@p tex.3d.v4.u32.f32 {%0, t1, t2, t3}, [%1, {%2, %3, %4, %4}];\n\t}"
+      : "=&r"(c)
+      : "l"(g.df_tex), "f"(gx + g.tex_bias[0]), "f"(gy + g.tex_bias[1]), "f"(gz + g.tex_bias[2]), "r"((int)need), "r"(skipped));
+  return (int)c;
+#else
+  return need ? tg_probe(g, gx, gy, gz) : skipped;
+#endif
+}
+
 struct TgClass {
   bool collide;
   uint32_t amb[4];
@@ -65,22 +81,50 @@ __device__ __forceinline__ TgPose tg_pose(const TgGrid& g, float bx, float by, f
   return p;
 }
 
+// Derived bounds (TG_DERIVED_BOUNDS, default on): sphere k of a rigid frame is not probed at all when the code already
+// read at its "source" point of the same frame (fetch_model.cuh tgm_k_src: one of the three big base spheres, or the
+// centre of the cull group's enclosing sphere) is >= thr.src_ge[k], i.e. proves the ball of radius
+// |c_k - c_src| + r_k + r_pt around the source free.  A skipped sphere reads TG_CODE_SKIPPED: free, never ambiguous.
+#define TG_CODE_SKIPPED (1 << 20)
+template <int K, int NS>
+__device__ __forceinline__ bool tg_need_probe(const TgThr& thr, const int (&src)[NS]) {
+#ifdef TG_NO_DERIVED_BOUNDS
+  return true;
+#else
+  constexpr int s = tgm_k_src(K);
+  if constexpr (s < 0 || s >= NS) {
+    return true;
+  } else {
+    return src[s] < thr.src_ge[K];
+  }
+#endif
+}
+
 // spheres [K0, K1) of a frame whose rotation is the base yaw only:  p_base = l + (tx, 0, tz).
 // All loads of the group are issued before the first classification (memory-level parallelism).
-template <int K0, int K1>
-__device__ __forceinline__ void tg_group_yaw(const TgGrid& g, const TgThr& thr, const TgPose& p, float gtx, float gty, float gtz,
-                                             TgClass& out) {
-  int code[K1 - K0];
-#pragma unroll
-  for (int k = K0; k < K1; ++k) {
-    const float4 l = TGM_K_SPH[k];
+template <int K, int K1, int K0, int NS>
+__device__ __forceinline__ void tg_probe_yaw(const TgGrid& g, const TgThr& thr, const TgPose& p, float gtx, float gty, float gtz,
+                                             const int (&src)[NS], int (&code)[K1 - K0]) {
+  if constexpr (K < K1) {
+    const float4 l = TGM_K_SPH[K];
     const float gx = fmaf(p.cs, l.x, fmaf(-p.sn, l.y, gtx));
     const float gy = fmaf(p.sn, l.x, fmaf(p.cs, l.y, gty));
     const float gz = fmaf(g.vpm, l.z, gtz);
-    code[k - K0] = tg_probe(g, gx, gy, gz);
+    code[K - K0] = tg_probe_if(g, tg_need_probe<K, NS>(thr, src), gx, gy, gz, TG_CODE_SKIPPED);
+    tg_probe_yaw<K + 1, K1, K0, NS>(g, thr, p, gtx, gty, gtz, src, code);
   }
+}
+template <int K0, int K1, int NS>
+__device__ __forceinline__ void tg_group_yaw(const TgGrid& g, const TgThr& thr, const TgPose& p, float gtx, float gty, float gtz,
+                                             const int (&src)[NS], TgClass& out, int* keep = nullptr) {
+  int code[K1 - K0];
+  tg_probe_yaw<K0, K1, K0, NS>(g, thr, p, gtx, gty, gtz, src, code);
 #pragma unroll
   for (int k = K0; k < K1; ++k) TG_CLASSIFY_ONE(k, code[k - K0]);
+  if (keep != nullptr) {
+#pragma unroll
+    for (int k = 0; k < (K1 - K0 < 3 ? K1 - K0 : 3); ++k) keep[k] = code[k];
+  }
 }
 
 // voxel-space affine map of an arm frame F (base_link frame) under base pose p
@@ -99,17 +143,22 @@ __device__ __forceinline__ void tg_vox_frame(const TgGrid& g, const TgPose& p, c
   V.gt[2] = g.vpm * F.t[2];
 }
 
-template <int K0, int K1>
-__device__ __forceinline__ void tg_group_arm(const TgGrid& g, const TgThr& thr, const TgVox& V, TgClass& out) {
-  int code[K1 - K0];
-#pragma unroll
-  for (int k = K0; k < K1; ++k) {
-    const float4 l = TGM_K_SPH[k];
+template <int K, int K1, int K0>
+__device__ __forceinline__ void tg_probe_arm(const TgGrid& g, const TgThr& thr, const TgVox& V, const int (&src)[1], int (&code)[K1 - K0]) {
+  if constexpr (K < K1) {
+    const float4 l = TGM_K_SPH[K];
     const float gx = fmaf(V.G[0], l.x, fmaf(V.G[1], l.y, fmaf(V.G[2], l.z, V.gt[0])));
     const float gy = fmaf(V.G[3], l.x, fmaf(V.G[4], l.y, fmaf(V.G[5], l.z, V.gt[1])));
     const float gz = fmaf(V.G[6], l.x, fmaf(V.G[7], l.y, fmaf(V.G[8], l.z, V.gt[2])));
-    code[k - K0] = tg_probe(g, gx, gy, gz);
+    code[K - K0] = tg_probe_if(g, tg_need_probe<K, 1>(thr, src), gx, gy, gz, TG_CODE_SKIPPED);
+    tg_probe_arm<K + 1, K1, K0>(g, thr, V, src, code);
   }
+}
+template <int K0, int K1>
+__device__ __forceinline__ void tg_group_arm(const TgGrid& g, const TgThr& thr, const TgVox& V, int bcode, TgClass& out) {
+  int code[K1 - K0];
+  const int src[1] = {bcode};
+  tg_probe_arm<K0, K1, K0>(g, thr, V, src, code);
 #pragma unroll
   for (int k = K0; k < K1; ++k) TG_CLASSIFY_ONE(k, code[k - K0]);
 }
@@ -117,11 +166,13 @@ __device__ __forceinline__ void tg_group_arm(const TgGrid& g, const TgThr& thr, 
 // Stage A: the 20 spheres that only depend on the base pose (base_link + torso_fixed), largest first.
 // Most colliding configurations are refuted by the first group of three.
 __device__ __forceinline__ void tg_stage_a(const TgGrid& g, const TgThr& thr, const TgPose& p, TgClass& out) {
-  tg_group_yaw<0, 3>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  int big[3];
+  const int none[1] = {0};
+  tg_group_yaw<0, 3, 1>(g, thr, p, p.gx0, p.gy0, 0.f, none, out, big);
   if (out.collide) return;
-  tg_group_yaw<3, 9>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  tg_group_yaw<3, 9, 3>(g, thr, p, p.gx0, p.gy0, 0.f, big, out);
   if (out.collide) return;
-  tg_group_yaw<9, 20>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  tg_group_yaw<9, 20, 3>(g, thr, p, p.gx0, p.gy0, 0.f, big, out);
 }
 
 // enclosing-sphere probes (cull groups, fetch_model.cuh TGM_BOUND): true = the whole group is free
@@ -131,12 +182,12 @@ __device__ __forceinline__ int tg_bound_code_yaw(const TgGrid& g, const TgPose& 
   return tg_probe(g, fmaf(p.cs, l.x, fmaf(-p.sn, l.y, gtx)), fmaf(p.sn, l.x, fmaf(p.cs, l.y, gty)), fmaf(g.vpm, l.z, gtz));
 }
 template <int B>
-__device__ __forceinline__ bool tg_bound_free_arm(const TgGrid& g, const TgThr& thr, const TgVox& V) {
+__device__ __forceinline__ int tg_bound_code_arm(const TgGrid& g, const TgVox& V) {
   const float4 l = TGM_BOUND[B];
   const float gx = fmaf(V.G[0], l.x, fmaf(V.G[1], l.y, fmaf(V.G[2], l.z, V.gt[0])));
   const float gy = fmaf(V.G[3], l.x, fmaf(V.G[4], l.y, fmaf(V.G[5], l.z, V.gt[1])));
   const float gz = fmaf(V.G[6], l.x, fmaf(V.G[7], l.y, fmaf(V.G[8], l.z, V.gt[2])));
-  return tg_probe(g, gx, gy, gz) >= thr.bound_ge[B];
+  return tg_probe(g, gx, gy, gz);
 }
 
 // Stage B: torso + head (35 spheres, base yaw + torso lift) and the 7-joint arm chain (56 spheres).
@@ -150,18 +201,19 @@ __device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, co
     const int b0 = tg_bound_code_yaw<0>(g, p, gtx1, gty1, gtz1);
     const int b1 = tg_bound_code_yaw<1>(g, p, gtx1, gty1, gtz1);
     const int b2 = tg_bound_code_yaw<2>(g, p, gtx1, gty1, gtz1);
-    tg_group_yaw<20, 28>(g, thr, p, gtx1, gty1, gtz1, out);
+    const int s0[1] = {b0}, s1[1] = {b1}, s2[1] = {b2};
+    tg_group_yaw<20, 28, 1>(g, thr, p, gtx1, gty1, gtz1, s0, out);
     if (out.collide) return;
     if (b0 < thr.bound_ge[0]) {
-      tg_group_yaw<28, 33>(g, thr, p, gtx1, gty1, gtz1, out);
+      tg_group_yaw<28, 33, 1>(g, thr, p, gtx1, gty1, gtz1, s0, out);
       if (out.collide) return;
     }
     if (b1 < thr.bound_ge[1]) {
-      tg_group_yaw<33, 44>(g, thr, p, gtx1, gty1, gtz1, out);
+      tg_group_yaw<33, 44, 1>(g, thr, p, gtx1, gty1, gtz1, s1, out);
       if (out.collide) return;
     }
     if (b2 < thr.bound_ge[2]) {
-      tg_group_yaw<44, 55>(g, thr, p, gtx1, gty1, gtz1, out);
+      tg_group_yaw<44, 55, 1>(g, thr, p, gtx1, gty1, gtz1, s2, out);
       if (out.collide) return;
     }
   }
@@ -172,46 +224,46 @@ __device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, co
   T.t[2] = tz;
   tg_frame_child(T, TGM_OFF_SHOULDER_PAN_X, TGM_OFF_SHOULDER_PAN_Y, TGM_OFF_SHOULDER_PAN_Z, 4, q[1], F);
   tg_vox_frame(g, p, F, V);
-  if (!tg_bound_free_arm<3>(g, thr, V)) {
-    tg_group_arm<55, 59>(g, thr, V, out);
+  if (const int bc = tg_bound_code_arm<3>(g, V); bc < thr.bound_ge[3]) {
+    tg_group_arm<55, 59>(g, thr, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(F, TGM_OFF_SHOULDER_LIFT_X, TGM_OFF_SHOULDER_LIFT_Y, TGM_OFF_SHOULDER_LIFT_Z, 3, q[2], H);
   tg_vox_frame(g, p, H, V);
-  if (!tg_bound_free_arm<4>(g, thr, V)) {
-    tg_group_arm<59, 66>(g, thr, V, out);
+  if (const int bc = tg_bound_code_arm<4>(g, V); bc < thr.bound_ge[4]) {
+    tg_group_arm<59, 66>(g, thr, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(H, TGM_OFF_UPPERARM_ROLL_X, TGM_OFF_UPPERARM_ROLL_Y, TGM_OFF_UPPERARM_ROLL_Z, 2, q[3], F);
   tg_vox_frame(g, p, F, V);
-  if (!tg_bound_free_arm<5>(g, thr, V)) {
-    tg_group_arm<66, 74>(g, thr, V, out);
+  if (const int bc = tg_bound_code_arm<5>(g, V); bc < thr.bound_ge[5]) {
+    tg_group_arm<66, 74>(g, thr, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(F, TGM_OFF_ELBOW_FLEX_X, TGM_OFF_ELBOW_FLEX_Y, TGM_OFF_ELBOW_FLEX_Z, 3, q[4], H);
   tg_vox_frame(g, p, H, V);
-  if (!tg_bound_free_arm<6>(g, thr, V)) {
-    tg_group_arm<74, 80>(g, thr, V, out);
+  if (const int bc = tg_bound_code_arm<6>(g, V); bc < thr.bound_ge[6]) {
+    tg_group_arm<74, 80>(g, thr, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(H, TGM_OFF_FOREARM_ROLL_X, TGM_OFF_FOREARM_ROLL_Y, TGM_OFF_FOREARM_ROLL_Z, 2, q[5], F);
   tg_vox_frame(g, p, F, V);
-  if (!tg_bound_free_arm<7>(g, thr, V)) {
-    tg_group_arm<80, 87>(g, thr, V, out);
+  if (const int bc = tg_bound_code_arm<7>(g, V); bc < thr.bound_ge[7]) {
+    tg_group_arm<80, 87>(g, thr, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(F, TGM_OFF_WRIST_FLEX_X, TGM_OFF_WRIST_FLEX_Y, TGM_OFF_WRIST_FLEX_Z, 3, q[6], H);
   tg_vox_frame(g, p, H, V);
-  if (!tg_bound_free_arm<8>(g, thr, V)) {
-    tg_group_arm<87, 93>(g, thr, V, out);
+  if (const int bc = tg_bound_code_arm<8>(g, V); bc < thr.bound_ge[8]) {
+    tg_group_arm<87, 93>(g, thr, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(H, TGM_OFF_WRIST_ROLL_X, TGM_OFF_WRIST_ROLL_Y, TGM_OFF_WRIST_ROLL_Z, 2, q[7], F);
   tg_vox_frame(g, p, F, V);
-  if (!tg_bound_free_arm<9>(g, thr, V)) {
-    tg_group_arm<93, 99>(g, thr, V, out);
+  if (const int bc = tg_bound_code_arm<9>(g, V); bc < thr.bound_ge[9]) {
+    tg_group_arm<93, 99>(g, thr, V, bc, out);
     if (out.collide) return;
-    tg_group_arm<99, 111>(g, thr, V, out);
+    tg_group_arm<99, 111>(g, thr, V, bc, out);
   }
 }
 

@@ -74,7 +74,7 @@ __device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& t
   if (live) {
     if (!g.empty) {
       const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
-      tg_stage_b(g, thr, p, cfg + 3, cl);
+      tg_stage_b<true>(g, thr, p, cfg + 3, cl);
     }
     if (!cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
     valid[idx] = cl.collide ? 0 : 1;
@@ -456,7 +456,7 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
       if (live && !g.empty) {
         const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
         if (!fixed_base) tg_stage_a(g, thr, p, cl);
-        if (!cl.collide) tg_stage_b(g, thr, p, cfg + 3, cl);
+        if (!cl.collide) tg_stage_b<false>(g, thr, p, cfg + 3, cl);  // derived bounds cost the edge kernel 8 %
       }
       if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
       hit = __any_sync(0xffffffffu, live && cl.collide);

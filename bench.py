@@ -44,6 +44,7 @@ def parse():
     p.add_argument("--cpu-sample", type=int, default=4_000_000, help="configurations per CPU-baseline sample")
     p.add_argument("--vpm", type=float, default=72.0, help="distance-grid voxels per metre (static cloud: the finer grid pays, sweep in profiles/)")
     p.add_argument("--cpm", type=float, default=0.0, help="narrow-phase cells per metre (0 = library default)")
+    p.add_argument("--cpmx", type=float, default=0.0, help="narrow-phase cells per metre along x (with --cpm = y/z; 0 = same as --cpm)")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu", action="store_true")
     return p.parse_args()
@@ -188,7 +189,9 @@ def main():
 
     # ---- world: rank 0 ingests the cloud and builds; the structure is broadcast ------------------
     w = CollisionWorld(device=local, max_points=1 << 20, voxels_per_metre=args.vpm, max_voxels=192 << 20)
-    if args.cpm > 0:
+    if args.cpm > 0 and args.cpmx > 0:
+        w.set_cell_shape(args.cpmx, args.cpm)
+    elif args.cpm > 0:
         w.set_cells_per_metre(args.cpm)
     t_build = t_bcast = 0.0
     cloud = None

@@ -66,10 +66,14 @@ int tg_env_build_host(tg_env* env, const float* xyz, int64_t n, void* stream);
  * synchronises (CUDA-graph capturable); points outside are ignored and counted
  * in tg_env_stats.  Pass NULL, NULL to return to automatic bounds.               */
 int tg_env_set_bounds(tg_env* env, const float* lo, const float* hi);
-/* Resolution of the narrow-phase cell grid used by the next build (cells per metre; default =
- * voxels_per_metre / 2).  Coarser cells mean fewer rows per ambiguous sphere but more candidate
+/* Resolution of the narrow-phase cell grid used by the next build (cells per metre, the same on all
+ * three axes; the default is anisotropic: 0.8 x voxels_per_metre along x, 0.2 x along y and z).  Coarser cells mean fewer rows per ambiguous sphere but more candidate
  * points per row.                                                                */
 int tg_env_set_cells_per_metre(tg_env* env, float cells_per_metre);
+/* Anisotropic cells: a cell row runs along x and is one contiguous point range, so the x resolution
+ * only tightens a sphere's chord (fewer candidate points) while the y/z resolution sets how many
+ * rows a sphere touches (two cell_start loads each).                                             */
+int tg_env_set_cell_shape(tg_env* env, float cells_per_metre_x, float cells_per_metre_yz);
 /* point radius used by the next build (add_pointcloud(point_radius=...), :205-209) */
 int tg_env_set_point_radius(tg_env* env, float point_radius);
 

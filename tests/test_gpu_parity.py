@@ -207,6 +207,29 @@ def test_point_radius_and_coarse_grid(tabletop):
     w.close()
 
 
+def test_cell_shape_does_not_change_verdicts_or_clearances(tabletop):
+    """The narrow-phase cell grid (isotropic, the anisotropic default, extreme aspect ratios, cells larger than the
+    largest sphere) only decides which candidate points are read: verdicts and clearances must be identical."""
+    cloud, w0, cc = tabletop
+    arm, base = synth.random_configs(20_000, seed=17, base_box=(-1, 1, -1, 1))
+    cl = cc.clearance(arm, base)
+    v0, c0 = w0.check_configs(_cuda(arm), _cuda(base), clearance=True)
+    _assert_verdicts(v0.cpu().numpy(), cl, "default cell shape")
+    a0, b0 = synth.random_configs(3000, seed=18, base_box=(-1, 1, -1, 1))
+    a1, _ = synth.random_configs(3000, seed=19)
+    e0 = w0.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b0))
+    for shape in ((20.0, 20.0), (160.0, 4.0), (3.0, 60.0), (2.0, 2.0), (200.0, 100.0)):
+        w = CollisionWorld(max_points=1 << 16)
+        w.set_cell_shape(*shape)
+        w.build(cloud)
+        v, c = w.check_configs(_cuda(arm), _cuda(base), clearance=True)
+        assert torch.equal(v, v0), shape
+        assert torch.equal(c, c0), shape
+        assert torch.equal(w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b0)), e0), shape
+        assert w.counters()["narrow_items"] > 0
+        w.close()
+
+
 def test_host_api_matches_device_api_and_chunks(room):
     cloud, w, cc = room
     arm, base = synth.random_configs(1_300_000, seed=21)              # > one 1M pipeline chunk

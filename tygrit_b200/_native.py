@@ -28,6 +28,7 @@ _SIGS = {
     "tg_env_set_bounds": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tg_env_set_point_radius": (C.c_int, [C.c_void_p, C.c_float]),
     "tg_env_set_cells_per_metre": (C.c_int, [C.c_void_p, C.c_float]),
+    "tg_env_set_cell_shape": (C.c_int, [C.c_void_p, C.c_float, C.c_float]),
     "tg_env_set_obstacles": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "tg_env_set_attachment": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "tg_env_export": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),

@@ -35,8 +35,9 @@ struct TgGrid {
   float slack;          // metres
   int window;           // W (voxels)
   // narrow-phase cell grid
-  float cpm;            // cells per metre
-  int cm[3];            // cell index = floor(x * cpm) - cm
+  float cpm;            // cells per metre along y and z
+  float cpmx;           // cells per metre along x (the row direction: finer x cells tighten the chord, coarser y/z cells mean fewer rows)
+  int cm[3];            // cell index = floor(p * cpm{x}) - cm
   int cnx, cny, cnz;
   float r_pt;           // cloud point radius
   int n_points;
@@ -121,7 +122,8 @@ struct tg_env {
   int64_t max_voxels;
   int64_t max_cells;
   float vpm_requested;
-  float cpm_requested;
+  float cpm_requested;   // y / z
+  float cpmx_requested;  // x
   float r_pt;
   int window;
   bool fixed_bounds;

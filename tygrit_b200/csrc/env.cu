@@ -91,7 +91,7 @@ k_count(const float* __restrict__ xyz, int n, TgGrid g, uint32_t* __restrict__ o
   if (isfinite(x) && isfinite(y) && isfinite(z)) {
     // df voxel: same arithmetic as the query side (one FMA-free multiply + magic add)
     const float fx = fmaf(x, g.vpm, g.bias[0]), fy = fmaf(y, g.vpm, g.bias[1]), fz = fmaf(z, g.vpm, g.bias[2]);
-    const int cx = (int)floorf(x * g.cpm) - g.cm[0];
+    const int cx = (int)floorf(x * g.cpmx) - g.cm[0];
     const int cy = (int)floorf(y * g.cpm) - g.cm[1];
     const int cz = (int)floorf(z * g.cpm) - g.cm[2];
     const bool in_df = fx >= TG_MAGIC && fx <= g.hi[0] && fy >= TG_MAGIC && fy <= g.hi[1] && fz >= TG_MAGIC && fz <= g.hi[2];
@@ -355,7 +355,7 @@ static void tg_compute_thresholds(const TgGrid& g, TgThr* thr) {
 
 // choose grid geometry for the cloud box [lo, hi]; returns false if it cannot fit
 static bool tg_plan_grids(tg_env* env, const float lo[3], const float hi[3], TgGrid* g) {
-  double vpm = env->vpm_requested, cpm = env->cpm_requested;
+  double vpm = env->vpm_requested, cpm = env->cpm_requested, cpmx = env->cpmx_requested;
   const double r_need = 0.24 + (double)env->r_pt;  // largest robot sphere + point radius
   for (int it = 0; it < 64; ++it) {
     const double slack = sqrt(3.0) / vpm + kEpsFp;
@@ -398,15 +398,18 @@ static bool tg_plan_grids(tg_env* env, const float lo[3], const float hi[3], TgG
     int cm[3], cn[3];
     double nc = 1;
     for (int a = 0; a < 3; ++a) {
-      cm[a] = (int)floor((double)lo[a] * cpm) - 1;
-      cn[a] = (int)floor((double)hi[a] * cpm) - cm[a] + 2;
+      const double ca = a == 0 ? cpmx : cpm;
+      cm[a] = (int)floor((double)lo[a] * ca) - 1;
+      cn[a] = (int)floor((double)hi[a] * ca) - cm[a] + 2;
       nc *= cn[a];
     }
     if (nc > (double)env->max_cells) {
       cpm *= 0.9;
+      cpmx *= 0.9;
       continue;
     }
     g->cpm = (float)cpm;
+    g->cpmx = (float)cpmx;
     for (int a = 0; a < 3; ++a) g->cm[a] = cm[a];
     g->cnx = cn[0]; g->cny = cn[1]; g->cnz = cn[2];
     return true;
@@ -486,7 +489,9 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
   env->max_voxels = max_voxels > 0 ? max_voxels : (int64_t)64 << 20;
   env->max_cells = env->max_voxels / 4;
   env->vpm_requested = voxels_per_metre;
-  env->cpm_requested = voxels_per_metre * 0.4f;  // 5 cm cells at the default 2 cm voxels (sweep in profiles/)
+  // cell rows run along x: 10 cm x 10 cm rows cut into 2.5 cm cells at the default 2 cm voxels (sweep: profiles/r01s22_cellshape_sweep.txt)
+  env->cpm_requested = voxels_per_metre * 0.2f;
+  env->cpmx_requested = voxels_per_metre * 0.8f;
   env->r_pt = point_radius;
   env->blob_capacity = TG_HEADER_BYTES + align256(env->max_voxels) + align256(4 * (env->max_cells + 1)) +
                        align256(16 * (size_t)max_points) + 1024;
@@ -568,6 +573,15 @@ extern "C" int tg_env_set_bounds(tg_env* env, const float* lo, const float* hi) 
 extern "C" int tg_env_set_cells_per_metre(tg_env* env, float cpm) {
   TG_CHECK_ARG(env != nullptr && cpm >= 2.f && cpm <= 100.f, "tg_env_set_cells_per_metre: need 2 <= cells_per_metre <= 100");
   env->cpm_requested = cpm;
+  env->cpmx_requested = cpm;
+  return TG_OK;
+}
+
+extern "C" int tg_env_set_cell_shape(tg_env* env, float cpm_x, float cpm_yz) {
+  TG_CHECK_ARG(env != nullptr && cpm_x >= 2.f && cpm_x <= 200.f && cpm_yz >= 2.f && cpm_yz <= 100.f,
+               "tg_env_set_cell_shape: need 2 <= cells_per_metre_x <= 200 and 2 <= cells_per_metre_yz <= 100");
+  env->cpmx_requested = cpm_x;
+  env->cpm_requested = cpm_yz;
   return TG_OK;
 }
 

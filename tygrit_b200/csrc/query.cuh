@@ -292,7 +292,7 @@ __device__ inline bool tg_sphere_hits_cloud(const TgGrid& g, float cx, float cy,
       const float rx2 = ry2 - dy * dy;
       if (rx2 < 0.f) continue;
       const float rx = sqrtf(rx2) + 1e-4f;
-      const int x0 = max((int)floorf((cx - rx) * g.cpm) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpm) - g.cm[0], g.cnx - 1);
+      const int x0 = max((int)floorf((cx - rx) * g.cpmx) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpmx) - g.cm[0], g.cnx - 1);
       if (x0 > x1) continue;
       const int row = (iz * g.cny + iy) * g.cnx;
       const uint32_t s = __ldg(g.cell_start + row + x0), e = __ldg(g.cell_start + row + x1 + 1);
@@ -325,7 +325,7 @@ __device__ inline float tg_sphere_clearance(const TgGrid& g, float cx, float cy,
       const float rx2 = ry2 - dy * dy;
       if (rx2 < 0.f || dz * dz + dy * dy > best2) continue;
       const float rx = sqrtf(rx2) + 1e-4f;
-      const int x0 = max((int)floorf((cx - rx) * g.cpm) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpm) - g.cm[0], g.cnx - 1);
+      const int x0 = max((int)floorf((cx - rx) * g.cpmx) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpmx) - g.cm[0], g.cnx - 1);
       if (x0 > x1) continue;
       const int row = (iz * g.cny + iy) * g.cnx;
       const uint32_t s = __ldg(g.cell_start + row + x0), e = __ldg(g.cell_start + row + x1 + 1);
@@ -385,7 +385,7 @@ __device__ __forceinline__ void tg_row_range(const TgGrid& g, const TgRows& w, f
   const float rx2 = Re * Re - dz * dz - dy * dy;
   if (rx2 < 0.f) return;
   const float rx = sqrtf(rx2) + 1e-4f;
-  const int x0 = max((int)floorf((cx - rx) * g.cpm) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpm) - g.cm[0], g.cnx - 1);
+  const int x0 = max((int)floorf((cx - rx) * g.cpmx) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpmx) - g.cm[0], g.cnx - 1);
   if (x0 > x1) return;
   const int row = (iz * g.cny + iy) * g.cnx;
   s = __ldg(g.cell_start + row + x0);

@@ -78,6 +78,10 @@ class CollisionWorld:
         """Resolution of the narrow-phase cell grid, used by the next :meth:`build`."""
         N.check(self._lib.tg_env_set_cells_per_metre(self._h, float(cpm)), "tg_env_set_cells_per_metre")
 
+    def set_cell_shape(self, cpm_x: float, cpm_yz: float) -> None:
+        """Anisotropic narrow-phase cells (x = the row direction), used by the next :meth:`build`."""
+        N.check(self._lib.tg_env_set_cell_shape(self._h, float(cpm_x), float(cpm_yz)), "tg_env_set_cell_shape")
+
     def set_bounds(self, lo=None, hi=None) -> None:
         if lo is None or hi is None:
             N.check(self._lib.tg_env_set_bounds(self._h, None, None), "tg_env_set_bounds")

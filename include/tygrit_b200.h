@@ -67,7 +67,7 @@ int tg_env_build_host(tg_env* env, const float* xyz, int64_t n, void* stream);
  * in tg_env_stats.  Pass NULL, NULL to return to automatic bounds.               */
 int tg_env_set_bounds(tg_env* env, const float* lo, const float* hi);
 /* Resolution of the narrow-phase cell grid used by the next build (cells per metre, the same on all
- * three axes; the default is anisotropic: 0.8 x voxels_per_metre along x, 0.2 x along y and z).  Coarser cells mean fewer rows per ambiguous sphere but more candidate
+ * three axes; the default is anisotropic: 64 cells per metre along x, 14 along y and z).  Coarser cells mean fewer rows per ambiguous sphere but more candidate
  * points per row.                                                                */
 int tg_env_set_cells_per_metre(tg_env* env, float cells_per_metre);
 /* Anisotropic cells: a cell row runs along x and is one contiguous point range, so the x resolution

@@ -489,9 +489,11 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
   env->max_voxels = max_voxels > 0 ? max_voxels : (int64_t)64 << 20;
   env->max_cells = env->max_voxels / 4;
   env->vpm_requested = voxels_per_metre;
-  // cell rows run along x: 10 cm x 10 cm rows cut into 2.5 cm cells at the default 2 cm voxels (sweep: profiles/r01s22_cellshape_sweep.txt)
-  env->cpm_requested = voxels_per_metre * 0.2f;
-  env->cpmx_requested = voxels_per_metre * 0.8f;
+  // cell rows run along x: 7.1 cm x 7.1 cm rows cut into 1.6 cm cells.  Absolute sizes, not multiples of the voxel: what they
+  // trade (rows touched against candidate points read) is set by the robot's sphere radii and the cloud's density
+  // (sweeps at 50 and 72 voxels/m: profiles/r01s22_cellshape_sweep*.txt, r01s22_cellshape_c1c2.txt)
+  env->cpm_requested = 14.f;
+  env->cpmx_requested = 64.f;
   env->r_pt = point_radius;
   env->blob_capacity = TG_HEADER_BYTES + align256(env->max_voxels) + align256(4 * (env->max_cells + 1)) +
                        align256(16 * (size_t)max_points) + 1024;

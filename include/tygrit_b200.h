@@ -85,6 +85,13 @@ int tg_env_set_obstacles(tg_env* env, const float* xyzr, int n, void* stream);
 int tg_env_set_attachment(tg_env* env, const float* xyzr, int n, const float* offset_pos,
                           const float* offset_quat, void* stream);
 
+/* Optional self-collision term of validate_whole_body_config (VAMP also tests the robot's
+ * spheres against each other; its pair list is not available, so the link pairs are the reference's own
+ * SELF_COLLISION_PAIRS, TyGrit/rl/train.py:78-107): when on, a configuration / edge sample also collides if two
+ * spheres of a listed link pair touch (|c_i - c_j| <= r_i + r_j), and the clearance output becomes
+ * min(cloud clearance, self clearance).  Off by default.                              */
+int tg_env_set_self_collision(tg_env* env, int on);
+
 /* Structure hand-off for multi-GPU (cloud structure replicated on every rank):
  * export gives a contiguous DEVICE blob + its size; import adopts a blob that was
  * broadcast into `blob` on this device.                                         */

@@ -38,14 +38,20 @@ def lib() -> C.CDLL:
         L.tgo_set_model.argtypes = [C.c_void_p, C.c_void_p]
         L.tgo_clearance_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_void_p]
         L.tgo_centres_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
-        L.tgo_check_configs_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int]
+        L.tgo_check_configs_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int]
         L.tgo_check_edges_f32.restype = C.c_int64
-        L.tgo_check_edges_f32.argtypes = [C.c_void_p] * 5 + [C.c_int64, C.c_int, C.c_double, C.c_void_p, C.c_int]
+        L.tgo_check_edges_f32.argtypes = [C.c_void_p] * 5 + [C.c_int64, C.c_int, C.c_double, C.c_void_p, C.c_int, C.c_int]
+        L.tgo_set_self_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        L.tgo_self_clearance_f64.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
         L.tgo_edge_clearance_f64.argtypes = [C.c_void_p] * 5 + [C.c_int64, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
         L.tgo_threads.restype = C.c_int
+        L.tgo_set_threads.argtypes = [C.c_int]
         xyzr = np.ascontiguousarray(fm.SPHERE_LOCAL, dtype=np.float64)
         link = np.ascontiguousarray(fm.SPHERE_LINK, dtype=np.int64)
         L.tgo_set_model(xyzr.ctypes.data, link.ctypes.data)
+        pi = np.ascontiguousarray(fm.SELF_PAIR_I, dtype=np.int64)
+        pj = np.ascontiguousarray(fm.SELF_PAIR_J, dtype=np.int64)
+        L.tgo_set_self_pairs(pi.ctypes.data, pj.ctypes.data, pi.shape[0])
         _lib = L
     return _lib
 
@@ -78,17 +84,22 @@ class CCloud:
         self._L.tgo_clearance_f64(self._h, arm.ctypes.data, base.ctypes.data, arm.shape[0], float(cap), out.ctypes.data)
         return out
 
-    def check_configs_f32(self, arm, base, threads: int = 0) -> np.ndarray:
+    def check_configs_f32(self, arm, base, threads: int = 0, self_collision: bool = False, naive: bool = False) -> np.ndarray:
+        """fp32 verdict path (the timed CPU baseline): coarse-to-fine along the link chain; ``naive`` = all 111
+        centres first, table order (the two forms give identical verdicts).  ``threads`` 0 = OpenMP default."""
         arm, base = _f32(arm, 8), _f32(base, 3)
         out = np.empty(arm.shape[0], dtype=np.uint8)
-        self._L.tgo_check_configs_f32(self._h, arm.ctypes.data, base.ctypes.data, arm.shape[0], out.ctypes.data, int(threads))
+        self._L.tgo_check_configs_f32(self._h, arm.ctypes.data, base.ctypes.data, arm.shape[0], out.ctypes.data, int(threads),
+                                      int(bool(self_collision)) | (2 if naive else 0))
         return out
 
-    def check_edges_f32(self, arm0, base0, arm1, base1, rake: int = 8, resolution: float = 32.0, threads: int = 0):
+    def check_edges_f32(self, arm0, base0, arm1, base1, rake: int = 8, resolution: float = 32.0, threads: int = 0,
+                        self_collision: bool = False):
         a0, b0, a1, b1 = _f32(arm0, 8), _f32(base0, 3), _f32(arm1, 8), _f32(base1, 3)
         out = np.empty(a0.shape[0], dtype=np.uint8)
         n = self._L.tgo_check_edges_f32(self._h, a0.ctypes.data, b0.ctypes.data, a1.ctypes.data, b1.ctypes.data,
-                                        a0.shape[0], int(rake), float(resolution), out.ctypes.data, int(threads))
+                                        a0.shape[0], int(rake), float(resolution), out.ctypes.data, int(threads),
+                                        int(bool(self_collision)))
         return out, int(n)
 
     def edge_clearance(self, arm0, base0, arm1, base1, rake: int = 8, resolution: float = 32.0, cap: float = 0.25):
@@ -109,5 +120,27 @@ def centres_f64(arm, base, head=None) -> np.ndarray:
     return out
 
 
+def self_clearance(arm) -> np.ndarray:
+    """fp64 ``min (|c_i - c_j| - r_i - r_j)`` over the sphere pairs of SELF_COLLISION_PAIRS (rl/train.py:78-107), (B,)."""
+    arm = _f32(arm, 8)
+    out = np.empty(arm.shape[0], dtype=np.float64)
+    lib().tgo_self_clearance_f64(arm.ctypes.data, arm.shape[0], out.ctypes.data)
+    return out
+
+
 def threads() -> int:
     return int(lib().tgo_threads())
+
+
+def set_threads(n: int) -> int:
+    """Set the OpenMP thread count of all later oracle calls; returns the count now in effect."""
+    lib().tgo_set_threads(int(n))
+    return threads()
+
+
+def host_threads() -> int:
+    """Host threads this process may use (``OMP_NUM_THREADS=1`` set by torchrun is deliberately ignored)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:  # pragma: no cover
+        return os.cpu_count() or 1

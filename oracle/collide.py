@@ -18,7 +18,11 @@ defined here, anchored on TyGrit's call sites:
    attachments (``:257-304``; spheres given in the attachment frame, which is the
    gripper_link frame composed with ``offset_pos`` / ``offset_quat [x,y,z,w]``)
    take part identically; attachment spheres are also tested against the cloud.
-5. No self-collision term and no joint-limit term.
+5. No joint-limit term.  The self-collision term is OPTIONAL and off by default (north_star lists
+   sphere-vs-point-cloud only): when enabled, a configuration also collides if two spheres of a
+   link pair in ``SELF_COLLISION_PAIRS`` (``TyGrit/rl/train.py:78-107``) touch,
+   ``self_clearance = min_{(i,j)} (|c_i - c_j| - r_i - r_j)``, valid iff ``> 0`` (VAMP's own pair
+   list is unavailable; the reference's RL reward uses exactly these link pairs).
 6. Edge a->b over the 11-vector ``[x, y, theta, q0..q7]`` (no angle wrapping):
    ``n = max(ceil(|b-a|_2 * resolution / rake), 1)``, samples
    ``t_k = k / (rake n)``, ``k = 1 .. rake n`` (end included, start excluded),
@@ -129,6 +133,19 @@ class CloudOracle:
     def edge_valid(self, arm0, base0, arm1, base1, attachment=None, **kw):
         cl, ns = self.edge_clearance(arm0, base0, arm1, base1, attachment, **kw)
         return cl > 0.0, cl, ns
+
+
+def self_clearance(arm8) -> np.ndarray:
+    """(B,) fp64 ``min_{(i,j) in pairs} (|c_i - c_j| - r_i - r_j)`` over the sphere pairs of
+    ``fetch_model.SELF_COLLISION_PAIRS`` (``TyGrit/rl/train.py:78-107``); base pose irrelevant, head = 0."""
+    arm = np.atleast_2d(np.asarray(arm8, dtype=np.float64))
+    out = np.empty(arm.shape[0])
+    r = fm.SPHERE_LOCAL[:, 3]
+    for s0 in range(0, arm.shape[0], 8192):
+        c = fk.sphere_centres(arm[s0:s0 + 8192], np.zeros((min(8192, arm.shape[0] - s0), 3)))
+        d = np.linalg.norm(c[:, fm.SELF_PAIR_I] - c[:, fm.SELF_PAIR_J], axis=-1) - r[fm.SELF_PAIR_I] - r[fm.SELF_PAIR_J]
+        out[s0:s0 + 8192] = d.min(axis=1)
+    return out
 
 
 def edge_vectors(arm8, base_xyt) -> np.ndarray:

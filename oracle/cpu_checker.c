@@ -12,7 +12,8 @@
  * FK follows TyGrit/kinematics/fetch/fk_numpy.py:65-155 and utils/transforms.py:116-127.
  *
  * Structure: dense uniform grid over the cloud box (counting sort), per-sphere scan of the cells that
- * overlap the sphere's box, early exit on the first hit, OpenMP over configurations.
+ * overlap the sphere's box, early exit on the first hit, OpenMP over configurations; the fp32 verdict path is
+ * coarse-to-fine (link by link along the chain, enclosing sphere before a link's spheres, largest first).
  *   tgo_check_*_f32   fp32 verdict path (what a CPU implementation would run; the timed baseline)
  *   tgo_clearance_f64 fp64 exact clearance (the oracle proper)
  */
@@ -42,12 +43,48 @@ static double SPH[NS][4];
 static int SPH_LINK[NS];
 static int model_set = 0;
 
+/* derived at load time for the coarse-to-fine fp32 path: spheres of each link, largest first, and one
+ * enclosing sphere per link (centre = mean of the link's sphere centres) */
+static int LINK_NSPH[NL];
+static int LINK_SPH[NL][32];
+static double LINK_BOUND[NL][4];
+/* optional self-collision term: sphere pairs of TyGrit/rl/train.py:78-107 SELF_COLLISION_PAIRS, grouped by link pair */
+#define MAX_SELF_PAIRS 4096
+static int SELF_I[MAX_SELF_PAIRS], SELF_J[MAX_SELF_PAIRS];
+static int n_self = 0;
+
 void tgo_set_model(const double* xyzr, const int64_t* link) {
   for (int i = 0; i < NS; ++i) {
     for (int k = 0; k < 4; ++k) SPH[i][k] = xyzr[4 * i + k];
     SPH_LINK[i] = (int)link[i];
   }
+  for (int l = 0; l < NL; ++l) {
+    int n = 0;
+    double m[3] = {0, 0, 0};
+    for (int i = 0; i < NS; ++i)
+      if (SPH_LINK[i] == l) { LINK_SPH[l][n++] = i; for (int k = 0; k < 3; ++k) m[k] += SPH[i][k]; }
+    LINK_NSPH[l] = n;
+    for (int a = 1; a < n; ++a) { /* insertion sort, radius descending (stable) */
+      const int v = LINK_SPH[l][a];
+      int b = a - 1;
+      while (b >= 0 && SPH[LINK_SPH[l][b]][3] < SPH[v][3]) { LINK_SPH[l][b + 1] = LINK_SPH[l][b]; --b; }
+      LINK_SPH[l][b + 1] = v;
+    }
+    double rb = 0;
+    for (int k = 0; k < 3; ++k) m[k] = n ? m[k] / n : 0;
+    for (int a = 0; a < n; ++a) {
+      const double* p = SPH[LINK_SPH[l][a]];
+      const double d = sqrt((p[0] - m[0]) * (p[0] - m[0]) + (p[1] - m[1]) * (p[1] - m[1]) + (p[2] - m[2]) * (p[2] - m[2])) + p[3];
+      if (d > rb) rb = d;
+    }
+    LINK_BOUND[l][0] = m[0]; LINK_BOUND[l][1] = m[1]; LINK_BOUND[l][2] = m[2]; LINK_BOUND[l][3] = rb * (1 + 1e-6) + 1e-6;
+  }
   model_set = 1;
+}
+
+void tgo_set_self_pairs(const int64_t* pi, const int64_t* pj, int64_t n) {
+  n_self = (int)(n < MAX_SELF_PAIRS ? n : MAX_SELF_PAIRS);
+  for (int k = 0; k < n_self; ++k) { SELF_I[k] = (int)pi[k]; SELF_J[k] = (int)pj[k]; }
 }
 
 typedef struct {
@@ -107,16 +144,19 @@ tgo_cloud* tgo_cloud_build(const float* xyz, int64_t n, double r_pt, double cell
 
 #define DEFINE_IMPL(T, SFX, SIN, COS, SQRT, PTS)                                                                  \
   /* link frames in base_link: R[15][9], t[15][3] */                                                              \
-  static void fk_links_##SFX(const T* q, T R[NL][9], T t[NL][3]) {                                               \
-    for (int k = 0; k < 9; ++k) R[0][k] = (k % 4 == 0) ? 1 : 0;                                                   \
-    t[0][0] = t[0][1] = t[0][2] = 0;                                                                             \
-    for (int i = 1; i < NL; ++i) {                                                                                \
+  static void fk_one_##SFX(int i, const T* q, T R[NL][9], T t[NL][3]) {                                          \
+    if (i == 0) {                                                                                                 \
+      for (int k = 0; k < 9; ++k) R[0][k] = (k % 4 == 0) ? 1 : 0;                                                 \
+      t[0][0] = t[0][1] = t[0][2] = 0;                                                                           \
+      return;                                                                                                     \
+    }                                                                                                             \
+    {                                                                                                             \
       const int p = LINK_PARENT[i], kind = LINK_KIND[i];                                                          \
       T o[3] = {(T)LINK_OFF[i][0], (T)LINK_OFF[i][1], (T)LINK_OFF[i][2]};                                         \
       const T qi = LINK_Q[i] >= 0 ? q[LINK_Q[i]] : 0;                                                             \
       if (kind == 1) o[2] += qi;                                                                                  \
       for (int r = 0; r < 3; ++r) t[i][r] = R[p][3 * r] * o[0] + R[p][3 * r + 1] * o[1] + R[p][3 * r + 2] * o[2] + t[p][r]; \
-      if (kind < 2) { memcpy(R[i], R[p], sizeof(T) * 9); continue; }                                              \
+      if (kind < 2) { memcpy(R[i], R[p], sizeof(T) * 9); return; }                                                \
       const T s = SIN(qi), c = COS(qi);                                                                           \
       const int a = kind == 2 ? 1 : (kind == 3 ? 2 : 0), b = kind == 2 ? 2 : (kind == 3 ? 0 : 1), k3 = 3 - a - b; \
       for (int r = 0; r < 3; ++r) {                                                                               \
@@ -126,6 +166,9 @@ tgo_cloud* tgo_cloud_build(const float* xyz, int64_t n, double r_pt, double cell
         R[i][3 * r + k3] = R[p][3 * r + k3];                                                                      \
       }                                                                                                           \
     }                                                                                                             \
+  }                                                                                                               \
+  static void fk_links_##SFX(const T* q, T R[NL][9], T t[NL][3]) {                                               \
+    for (int i = 0; i < NL; ++i) fk_one_##SFX(i, q, R, t);                                                        \
   }                                                                                                               \
   /* world sphere centres (head joints given), out[111][3] */                                                     \
   static void centres_##SFX(const T* arm, const T* base, T hp, T ht, T out[NS][3]) {                             \
@@ -205,8 +248,27 @@ void tgo_centres_f64(const float* arm, const float* base, const float* head, int
   }
 }
 
+/* ---- optional self-collision term (TyGrit/rl/train.py:78-107 pairs): base_link frame, head = 0 ------ */
+void tgo_self_clearance_f64(const float* arm, int64_t B, double* out) {
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < B; ++i) {
+    double a[8], b[3] = {0, 0, 0}, ctr[NS][3];
+    for (int k = 0; k < 8; ++k) a[k] = arm[8 * i + k];
+    centres_f64(a, b, 0.0, 0.0, ctr);
+    double best = 1e300;
+    for (int k = 0; k < n_self; ++k) {
+      const int p = SELF_I[k], q = SELF_J[k];
+      const double dx = ctr[p][0] - ctr[q][0], dy = ctr[p][1] - ctr[q][1], dz = ctr[p][2] - ctr[q][2];
+      const double v = sqrt(dx * dx + dy * dy + dz * dz) - SPH[p][3] - SPH[q][3];
+      if (v < best) best = v;
+    }
+    out[i] = best;
+  }
+}
+
 /* ---- fp32 verdict path: the timed CPU baseline ---------------------------------------------------- */
-static int config_valid_f32(const tgo_cloud* c, const float* arm, const float* base) {
+/* Naive form (all 111 centres first, table order): kept as the second opinion of the tests. */
+static int config_valid_naive_f32(const tgo_cloud* c, const float* arm, const float* base) {
   float ctr[NS][3];
   centres_f32(arm, base, 0.f, 0.f, ctr);
   for (int j = 0; j < NS; ++j) {
@@ -216,12 +278,64 @@ static int config_valid_f32(const tgo_cloud* c, const float* arm, const float* b
   return 1;
 }
 
-void tgo_check_configs_f32(const tgo_cloud* c, const float* arm, const float* base, int64_t B, uint8_t* valid, int threads) {
+/* Coarse-to-fine form, what a tuned scalar CPU checker does (and what VAMP's generated fkcc does per SIMD lane,
+ * SURVEY.md 9.3): the link chain is advanced one link at a time and each link is tested as soon as its frame
+ * exists - enclosing sphere first, then its spheres largest first - so a colliding base never pays for the arm FK.
+ * Same fp32 sphere test, same verdicts as the naive form (the enclosing-sphere test is conservative). */
+static int config_valid_f32(const tgo_cloud* c, const float* arm, const float* base, int self_on) {
+  float q[10], R[NL][9], t[NL][3], W[NS][3];
+  for (int k = 0; k < 8; ++k) q[k] = arm[k];
+  q[8] = q[9] = 0.f;
+  const float cb = cosf(base[2]), sb = sinf(base[2]);
+  const float rpt = (float)c->r_pt;
+  for (int l = 0; l < NL; ++l) {
+    fk_one_f32(l, q, R, t);
+    const int n = LINK_NSPH[l];
+    if (n == 0) continue;
+    int need = 1;
+    if (n >= 3 && !self_on) { /* with the self term on, the world centres are needed later anyway */
+      const float lx = (float)LINK_BOUND[l][0], ly = (float)LINK_BOUND[l][1], lz = (float)LINK_BOUND[l][2];
+      const float bx = R[l][0] * lx + R[l][1] * ly + R[l][2] * lz + t[l][0];
+      const float by = R[l][3] * lx + R[l][4] * ly + R[l][5] * lz + t[l][1];
+      const float bz = R[l][6] * lx + R[l][7] * ly + R[l][8] * lz + t[l][2];
+      const float w[3] = {cb * bx - sb * by + base[0], sb * bx + cb * by + base[1], bz};
+      need = sphere_clear_f32(c, w, (float)LINK_BOUND[l][3] + rpt, 0.f, 1) < 0.f;
+    }
+    if (!need) continue;
+    for (int a = 0; a < n; ++a) {
+      const int j = LINK_SPH[l][a];
+      const float lx = (float)SPH[j][0], ly = (float)SPH[j][1], lz = (float)SPH[j][2];
+      const float bx = R[l][0] * lx + R[l][1] * ly + R[l][2] * lz + t[l][0];
+      const float by = R[l][3] * lx + R[l][4] * ly + R[l][5] * lz + t[l][1];
+      const float bz = R[l][6] * lx + R[l][7] * ly + R[l][8] * lz + t[l][2];
+      W[j][0] = cb * bx - sb * by + base[0];
+      W[j][1] = sb * bx + cb * by + base[1];
+      W[j][2] = bz;
+      if (sphere_clear_f32(c, W[j], (float)SPH[j][3] + rpt, 0.f, 1) < 0.f) return 0;
+    }
+  }
+  if (self_on)
+    for (int k = 0; k < n_self; ++k) {
+      const int p = SELF_I[k], r = SELF_J[k];
+      const float dx = W[p][0] - W[r][0], dy = W[p][1] - W[r][1], dz = W[p][2] - W[r][2];
+      const float rr = (float)SPH[p][3] + (float)SPH[r][3];
+      if (dx * dx + dy * dy + dz * dz <= rr * rr) return 0;
+    }
+  return 1;
+}
+
+/* mode bit 0: self-collision term on; bit 1: naive form (no staging) */
+void tgo_check_configs_f32(const tgo_cloud* c, const float* arm, const float* base, int64_t B, uint8_t* valid, int threads, int mode) {
 #ifdef _OPENMP
   if (threads > 0) omp_set_num_threads(threads);
 #endif
+  if (mode & 2) {
 #pragma omp parallel for schedule(dynamic, 64)
-  for (int64_t i = 0; i < B; ++i) valid[i] = (uint8_t)config_valid_f32(c, arm + 8 * i, base + 3 * i);
+    for (int64_t i = 0; i < B; ++i) valid[i] = (uint8_t)config_valid_naive_f32(c, arm + 8 * i, base + 3 * i);
+    return;
+  }
+#pragma omp parallel for schedule(dynamic, 256)
+  for (int64_t i = 0; i < B; ++i) valid[i] = (uint8_t)config_valid_f32(c, arm + 8 * i, base + 3 * i, mode & 1);
 }
 
 /* edges: n = max(ceil(|d| * resolution / rake), 1) in fp64 (order x,y,theta,q0..q7); samples k/(rake n) */
@@ -235,7 +349,7 @@ static int64_t edge_total(const float* a0, const float* b0, const float* a1, con
 }
 
 int64_t tgo_check_edges_f32(const tgo_cloud* c, const float* arm0, const float* base0, const float* arm1, const float* base1,
-                            int64_t E, int rake, double resolution, uint8_t* valid, int threads) {
+                            int64_t E, int rake, double resolution, uint8_t* valid, int threads, int mode) {
 #ifdef _OPENMP
   if (threads > 0) omp_set_num_threads(threads);
 #endif
@@ -254,7 +368,7 @@ int64_t tgo_check_edges_f32(const tgo_cloud* c, const float* arm0, const float* 
         float a[8], b[3];
         for (int j = 0; j < 8; ++j) a[j] = arm0[8 * e + j] + t * (arm1[8 * e + j] - arm0[8 * e + j]);
         for (int j = 0; j < 3; ++j) b[j] = base0[3 * e + j] + t * (base1[3 * e + j] - base0[3 * e + j]);
-        ok = config_valid_f32(c, a, b);
+        ok = config_valid_f32(c, a, b, mode & 1);
       }
     valid[e] = (uint8_t)ok;
   }
@@ -284,6 +398,15 @@ void tgo_edge_clearance_f64(const tgo_cloud* c, const float* arm0, const float* 
   }
 }
 
+/* OpenMP thread count for every later call (0 = leave as is); torchrun exports OMP_NUM_THREADS=1, which the
+ * CPU baseline must not inherit silently */
+void tgo_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
 int tgo_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

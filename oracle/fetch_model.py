@@ -125,3 +125,31 @@ SPHERE_LINK = np.concatenate(
 SPHERE_LOCAL = np.vstack(list(SPHERES_BY_LINK.values()))  # (111, 4) x,y,z,r
 N_SPHERES = SPHERE_LOCAL.shape[0]
 assert N_SPHERES == 111
+
+# Non-adjacent link pairs that can physically self-collide (TyGrit/rl/train.py:78-107,
+# SELF_COLLISION_PAIRS).  head_tilt_link carries no spheres, so its eight pairs contribute
+# no sphere-sphere test; the remaining 18 link pairs expand to 1,764 sphere pairs.
+SELF_COLLISION_PAIRS = tuple(
+    [("head_pan_link", b) for b in ("upperarm_roll_link", "elbow_flex_link", "forearm_roll_link", "wrist_flex_link",
+                                    "wrist_roll_link", "gripper_link", "l_gripper_finger_link", "r_gripper_finger_link")]
+    + [("head_tilt_link", b) for b in ("upperarm_roll_link", "elbow_flex_link", "forearm_roll_link", "wrist_flex_link",
+                                       "wrist_roll_link", "gripper_link", "l_gripper_finger_link", "r_gripper_finger_link")]
+    + [(a, b) for a in ("base_link", "torso_lift_link")
+       for b in ("wrist_flex_link", "wrist_roll_link", "gripper_link", "l_gripper_finger_link", "r_gripper_finger_link")]
+)
+
+
+def _self_sphere_pairs():
+    ii, jj = [], []
+    for a, b in SELF_COLLISION_PAIRS:
+        ia = np.flatnonzero(SPHERE_LINK == LINK_INDEX[a])
+        ib = np.flatnonzero(SPHERE_LINK == LINK_INDEX[b])
+        for i in ia:
+            for j in ib:
+                ii.append(i)
+                jj.append(j)
+    return np.asarray(ii, dtype=np.int64), np.asarray(jj, dtype=np.int64)
+
+
+SELF_PAIR_I, SELF_PAIR_J = _self_sphere_pairs()        # (1764,) sphere indices (reference order)
+assert SELF_PAIR_I.shape[0] == 1764

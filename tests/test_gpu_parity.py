@@ -528,3 +528,108 @@ def test_synth_depth_kernel_matches_numpy_twin():
     ok = got > 0
     assert 0.9 < ok.mean() < 0.995                                    # ~2 % invalid pixels
     assert np.median(np.abs(got[ok] - ref[ok])) < 1e-4 and (np.abs(got[ok] - ref[ok]) < 1e-2).mean() > 0.98
+
+
+# ------------------------------------------------------------------ the benchmarked configuration itself
+@pytest.fixture(scope="module")
+def bench_world():
+    """What bench.py times: the 500k-point room cloud with the distance grid at 72 voxels/m."""
+    cloud = synth.room_cloud(500_000)
+    w = CollisionWorld(max_points=1 << 20, voxels_per_metre=72.0, max_voxels=192 << 20)
+    w.build(_cuda(cloud))
+    return cloud, w, cchecker.CCloud(cloud)
+
+
+def test_bench_configuration_500k_72vpm_vs_fp64_oracle(bench_world):
+    cloud, w, cc = bench_world
+    dev = torch.device("cuda", 0)
+    arm, base = synth.device_configs(300_000, seed=42, device=dev)       # bench.py's own generator and seed
+    valid = w.check_configs(arm, base).cpu().numpy()
+    cl = cc.clearance(arm.cpu().numpy(), base.cpu().numpy(), cap=1e-3)
+    _assert_verdicts(valid, cl, "bench C4 sample")
+    assert 0.1 < valid.mean() < 0.3
+    # the planner-like batch of bench.py's free_workload leg
+    f_arm, f_base, floor = synth.free_base_configs(w, 200_000, seed=42, device=dev)
+    f_valid = w.check_configs(f_arm, f_base).cpu().numpy()
+    _assert_verdicts(f_valid, cc.clearance(f_arm.cpu().numpy(), f_base.cpu().numpy(), cap=1e-3), "bench free workload")
+    assert f_valid.mean() > 0.5 and 0.05 < floor < 0.9
+    # and edges on the same world
+    a0, b0, a1, b1 = synth.random_edges(3000, seed=5)
+    ev = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1)).cpu().numpy()
+    ecl, _ = cc.edge_clearance(a0, b0, a1, b1, cap=1e-3)
+    _assert_verdicts(ev, ecl, "bench-world edges")
+
+
+def test_self_collision_term_vs_oracle(tabletop):
+    """Optional sphere-vs-sphere term over the reference's SELF_COLLISION_PAIRS (rl/train.py:78-107): off by default,
+    on = verdict of min(cloud clearance, self clearance); clearance output follows; edges sample it too."""
+    cloud, w, cc = tabletop
+    arm, base = synth.random_configs(40_000, seed=23, base_box=(-1, 1, -1, 1))
+    cl_cloud = cc.clearance(arm, base)
+    cl_self = cchecker.self_clearance(arm)
+    np.testing.assert_allclose(cl_self[:2000], collide.self_clearance(arm[:2000]), atol=1e-12)
+    assert 0.05 < (cl_self <= 0).mean() < 0.3
+    off = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    try:
+        w.set_self_collision(True)
+        on, clr = w.check_configs(_cuda(arm), _cuda(base), clearance=True)
+        on, clr = on.cpu().numpy(), clr.cpu().numpy()
+        a0, b0, a1, b1 = synth.random_edges(1500, seed=24, base_box=(-1, 1, -1, 1), rrt_like=True)
+        ev = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1)).cpu().numpy()
+        # empty world: only the self term is left
+        e = CollisionWorld(max_points=1024)
+        e.build(np.empty((0, 3), np.float32))
+        e.set_self_collision(True)
+        only_self = e.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+        tuck = np.array([synth.TUCK_ARM], np.float32)
+        assert e.check_configs(_cuda(tuck), _cuda(np.zeros((1, 3), np.float32))).item() == 1   # test/test_planner.py:72-78
+    finally:
+        w.set_self_collision(False)
+    _assert_verdicts(off, cl_cloud, "self off")
+    total = np.minimum(cl_cloud, cl_self)
+    _assert_verdicts(on, total, "self on")
+    _assert_verdicts(only_self, cl_self, "self only")
+    assert (off != on).sum() > 100                                      # the term decided something
+    np.testing.assert_allclose(clr, np.minimum(total, 0.25), atol=3e-6)
+    # edge oracle: min over the samples of min(cloud, self)
+    ea, eb = collide.edge_vectors(a0, b0), collide.edge_vectors(a1, b1)
+    n = collide.edge_n(ea, eb)
+    ecl = np.empty(len(ea))
+    for i in range(len(ea)):
+        q = collide.edge_samples(ea[i], eb[i], int(n[i])).astype(np.float32)
+        ecl[i] = min(cc.clearance(q[:, 3:], q[:, :3]).min(), cchecker.self_clearance(q[:, 3:]).min())
+    _assert_verdicts(ev, ecl, "self on, edges")
+    assert np.array_equal(w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy(), off)   # and off again
+
+
+def test_streaming_self_filter_full_resolution_vs_oracle():
+    """BASELINE config[2] at its real frame size: k_self_filter_stream (the kernel C3 times) at 480 x 640 compared with
+    the oracle directly (oracle/ingest.py = kinematics/robot_filter.py + utils/depth.py), not with the generic kernel."""
+    from tygrit_b200 import _native as N
+
+    H, W, S = 480, 640, 3
+    K = synth.HEAD_CAMERA_K.copy()
+    states = synth.random_states(S, seed=31)
+    states[:, 11] = np.clip(states[:, 11], -0.6, 0.6)
+    states[:, 12] = 0.9
+    st = _cuda(states)
+    bx = _cuda(np.array([[*lo, *hi] for lo, hi in synth.room_boxes()], np.float32))
+    depth = torch.empty(S, H, W, device="cuda")
+    N.check(N.lib().tg_synth_depth(st.data_ptr(), S, bx.data_ptr(), bx.shape[0], H, W, np.ascontiguousarray(K).ctypes.data,
+                                   0.0, 5, depth.data_ptr(), None), "tg_synth_depth")
+    mask = engine.self_filter_depth(depth, K, st, 0.08, (0.2, 3.0), 1).cpu().numpy().astype(bool)   # mask only, stride 1: streaming kernel
+    d_np = depth.cpu().numpy()
+    removed = 0
+    for s in range(S):
+        T = ofk.camera_pose(states[s:s + 1, 3:11], states[s:s + 1, 11:13], states[s:s + 1, :3])[0]
+        pw, keep = oin.depth_to_world(d_np[s], K, T, (0.2, 3.0), 1)
+        c64 = ofk.sphere_centres(states[s:s + 1, 3:11], states[s:s + 1, :3], states[s:s + 1, 11:13])[0]
+        signed = oin.self_filter_signed_band(pw, c64, 0.08)
+        expect = np.zeros(keep.shape, bool)
+        expect[keep] = signed >= 0
+        decisive = np.ones(keep.shape, bool)
+        decisive[keep] = np.abs(signed) > BAND
+        assert np.array_equal(mask[s][decisive], expect[decisive])
+        assert not mask[s][~keep].any()
+        removed += int((signed < 0).sum())
+    assert removed > 1000

@@ -163,3 +163,55 @@ def test_disc_rasteriser_known_answer_and_cv2():
             got = np.zeros((60, 80), np.uint8)
             oocc.draw_disc(got, c[0], c[1], r)
             assert np.array_equal(ref, got)
+
+
+def test_coarse_to_fine_cpu_port_equals_naive_form():
+    """The timed CPU baseline (link by link, enclosing sphere first, early exit) gives the verdicts of the naive form
+    (all 111 centres, table order) and agrees with the fp64 clearance outside the band."""
+    from oracle import cchecker
+    from tygrit_b200 import synth
+
+    cloud = synth.room_cloud(60_000)
+    cc = cchecker.CCloud(cloud)
+    arm, base = synth.random_configs(30_000, seed=11)
+    staged = cc.check_configs_f32(arm, base)
+    naive = cc.check_configs_f32(arm, base, naive=True)
+    assert np.array_equal(staged, naive) and 0.05 < staged.mean() < 0.6
+    cl = cc.clearance(arm, base, cap=1e-3)
+    d = np.abs(cl) > 1e-5
+    assert np.array_equal(staged.astype(bool)[d], (cl > 0)[d])
+    one = cc.check_configs_f32(arm[:2000], base[:2000], threads=1)
+    assert np.array_equal(one, staged[:2000])
+    assert cchecker.set_threads(2) == 2 and cchecker.set_threads(cchecker.host_threads()) == cchecker.host_threads()
+
+
+def test_self_collision_oracle():
+    """Self-collision term: pair list = TyGrit/rl/train.py:78-107 (checked against the reference file when present),
+    numpy and C restatements agree, and the reference tests' tuck configuration stays valid."""
+    import os
+
+    from oracle import cchecker, collide, fetch_model as fm
+    from tygrit_b200 import fetch_model as pm, synth
+
+    assert set(fm.SELF_COLLISION_PAIRS) == set(pm.SELF_COLLISION_PAIRS) and len(fm.SELF_COLLISION_PAIRS) == 26
+    ref = "/root/reference/TyGrit/rl/train.py"
+    if os.path.exists(ref):
+        import ast
+
+        tree = ast.parse(open(ref).read())
+        pairs = None
+        for node in ast.walk(tree):
+            tgt = getattr(node, "target", None) or (node.targets[0] if isinstance(node, ast.Assign) else None)
+            if isinstance(node, (ast.Assign, ast.AnnAssign)) and getattr(tgt, "id", "") == "SELF_COLLISION_PAIRS":
+                pairs = ast.literal_eval(node.value)
+        assert pairs is not None and set(map(tuple, pairs)) == set(fm.SELF_COLLISION_PAIRS)
+    arm, _ = synth.random_configs(3000, seed=5)
+    a = cchecker.self_clearance(arm)
+    b = collide.self_clearance(arm)
+    np.testing.assert_allclose(a, b, atol=1e-12)
+    assert 0.05 < (a <= 0).mean() < 0.3
+    assert collide.self_clearance(np.array([synth.TUCK_ARM]))[0] > 0.005
+    cc = cchecker.CCloud(np.empty((0, 3), np.float32))
+    v = cc.check_configs_f32(arm, np.zeros((len(arm), 3), np.float32), self_collision=True)
+    d = np.abs(a) > 1e-5
+    assert np.array_equal(v.astype(bool)[d], (a > 0)[d])

@@ -21,7 +21,13 @@ want = ['Kernel Name', 'gpu__time_duration.sum', 'launch__registers_per_thread',
         'smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio',
         'smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio',
         'smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio',
-        'sm__cycles_elapsed.max']
+        'sm__cycles_elapsed.max',
+        # the resource DESIGN.md 5.2 names as binding for the probe kernels: L1-miss requests an SM can send to L2
+        'l1tex__m_l1tex2xbar_req_cycles_active.avg.pct_of_peak_sustained_elapsed', 'l1tex__m_xbar2l1tex_read_sectors.sum',
+        'lts__t_sectors.sum', 'lts__t_requests.sum', 'lts__t_sectors_srcunit_tex.sum', 'l1tex__t_requests_pipe_tex.sum',
+        'l1tex__t_sectors_pipe_tex.sum', 'sm__inst_executed_pipe_tex.avg.pct_of_peak_sustained_active',
+        'smsp__average_warps_issue_stalled_tex_throttle_per_issue_active.ratio',
+        'smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio']
 for w in want:
     if w in hdr:
         i = hdr.index(w)

@@ -31,6 +31,7 @@ _SIGS = {
     "tg_env_set_cell_shape": (C.c_int, [C.c_void_p, C.c_float, C.c_float]),
     "tg_env_set_obstacles": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "tg_env_set_attachment": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "tg_env_set_self_collision": (C.c_int, [C.c_void_p, C.c_int]),
     "tg_env_export": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "tg_env_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "tg_env_blob_capacity": (C.c_size_t, [C.c_void_p]),

@@ -69,7 +69,9 @@ def _build(LIB: str, OBJDIR: str, extra: list[str], force: bool, verbose: bool) 
             print(out, file=sys.stderr)
         if p.returncode:
             raise RuntimeError("nvcc failed for " + cmd[-3])
-    link = [nvcc_path(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs]
+    # shared cudart (the toolkit's libcudart.so.12, the same soname torch loads): the library then holds only its own code
+    link = [nvcc_path(), "-shared", "--cudart", "shared", "-Xlinker", "-rpath=/usr/local/cuda/lib64", "-gencode",
+            "arch=compute_100a,code=sm_100a", "-o", LIB, *objs]
     subprocess.run(link, check=True)
     return LIB
 

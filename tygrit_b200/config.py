@@ -25,6 +25,11 @@ class B200PlannerConfig(PlannerConfig):
     interpolation_steps: int = 16
     interpolation_density: float = 0.08
     bounds_padding: float = 0.1
+    fcit_max_iterations: int = 200
+    fcit_max_samples: int = 8192
+    fcit_batch_size: int = 4096
+    fcit_reverse_weight: float = 10.0
+    fcit_optimize: bool = True
     # B200 engine
     device: int = 0
     max_points: int = 1 << 20

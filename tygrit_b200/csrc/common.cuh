@@ -20,6 +20,7 @@
 #define TG_MAGIC_BITS 0x4B000000u  // bit pattern of 2^23
 #define TG_HEADER_BYTES 4096
 #define TG_CLEARANCE_CAP 0.25f
+#define TG_FLAG_SELF 1  // tg_env.flags: self-collision term on (tg_env_set_self_collision)
 #define TG_HOST_MAX_CHUNKS 4096
 #define TG_HOST_SMALL 16384  // host batches up to this size go through one packed H2D copy and one D2H copy
 
@@ -153,6 +154,7 @@ struct tg_env {
   unsigned* queue_count;
   unsigned queue_capacity;
   unsigned queue_limit;  // test hook: 0 = use the whole queue
+  int flags;             // TG_FLAG_*: optional terms evaluated by their own kernels after the cloud verdicts
   TgCounters* counters_dev;
   TgCounters* counters_host;  // pinned
   int64_t launches;

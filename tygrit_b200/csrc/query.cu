@@ -72,6 +72,7 @@ __device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& t
   tg_class_clear(cl);
   cl.amb[0] = amb0;
   if (live) {
+    TG_STAT_LANE(12, 1);  // configurations that reach stage B (arm FK executed)
     if (!g.empty) {
       const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
       tg_stage_b<true>(g, thr, p, cfg + 3, cl);
@@ -520,7 +521,7 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
 // clearance (optional output of tg_check_configs): exact, clipped at TG_CLEARANCE_CAP
 __global__ void __launch_bounds__(TG_BLOCK)
 k_clearance(const TgGrid g, const TgExtras* __restrict__ ex, const float* __restrict__ arm, const float* __restrict__ base,
-            int B, float* __restrict__ clearance) {
+            int B, float* __restrict__ clearance, int flags) {
   const int i = blockIdx.x * TG_BLOCK + threadIdx.x;
   if (i >= B) return;
   float q10[10];
@@ -554,7 +555,57 @@ k_clearance(const TgGrid g, const TgExtras* __restrict__ ex, const float* __rest
       best = fminf(best, sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) - c.w - ob.w);
     }
   }
+  if (flags & TG_FLAG_SELF) best = tg_self_clearance(arm + 8 * (size_t)i, best, false);
   clearance[i] = best;
+}
+
+// Optional self-collision term (tg_env_set_self_collision), as passes of their own after the cloud verdicts so that the
+// hot kernels stay untouched: a configuration / edge that is still valid is cleared when two spheres of a listed link
+// pair touch.  Edges repeat k_check_edges' sampling (same n, same t_k).
+__global__ void __launch_bounds__(TG_BLOCK) k_self_configs(const float* __restrict__ arm, int B, uint8_t* __restrict__ valid) {
+  const int i = blockIdx.x * TG_BLOCK + threadIdx.x;
+  if (i >= B || valid[i] == 0) return;
+  float q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) q[k] = arm[8 * (size_t)i + k];
+  if (tg_self_hit(q)) valid[i] = 0;
+}
+
+__global__ void __launch_bounds__(TG_BLOCK)
+k_self_edges(const float* __restrict__ arm0, const float* __restrict__ base0, const float* __restrict__ arm1,
+             const float* __restrict__ base1, int E, int rake, float resolution, uint8_t* __restrict__ valid) {
+  const unsigned lane = threadIdx.x & 31;
+  const int e = blockIdx.x * (TG_BLOCK / 32) + (threadIdx.x >> 5);
+  if (e >= E || valid[e] == 0) return;  // warp-uniform
+  float a[8], d[8];
+  double s2 = 0.0;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const double dk = (double)__ldg(base1 + 3 * (size_t)e + k) - (double)__ldg(base0 + 3 * (size_t)e + k);
+    s2 = s2 + dk * dk;
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    a[k] = __ldg(arm0 + 8 * (size_t)e + k);
+    const float b = __ldg(arm1 + 8 * (size_t)e + k);
+    const double dk = (double)b - (double)a[k];
+    s2 = s2 + dk * dk;
+    d[k] = b - a[k];
+  }
+  const double nn = ceil(sqrt(s2) * ((double)resolution / (double)rake));
+  const int n = nn < 1.0 ? 1 : (nn > 1.0e6 ? 1000000 : (int)nn);
+  const int total = rake * n, rounds = (total + 31) >> 5;
+  const float inv_total = 1.0f / (float)total;
+  bool hit = false;
+  for (int j = 0; j < rounds && !hit; ++j) {
+    const int k = (int)lane * rounds + j + 1;
+    float q[8];
+    const float t = (float)k * inv_total;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) q[c] = fmaf(t, d[c], a[c]);
+    hit = __any_sync(0xffffffffu, k <= total && tg_self_hit(q));
+  }
+  if (hit && lane == 0) valid[e] = 0;
 }
 
 __global__ void k_fill_u8(uint8_t* p, int n, uint8_t v) {
@@ -587,6 +638,13 @@ static inline TgQueue tg_queue_slot(const tg_env* env, int slot) {
   if (slot < 0) return TgQueue{env->items, env->queue_count, cap};
   const unsigned half = env->queue_capacity / 2;
   return TgQueue{env->items + (size_t)slot * half, env->queue_count + 4 * slot, cap < half ? cap : half};
+}
+
+// Self-collision term (off by default): see tg_self_clearance in query.cuh.
+extern "C" int tg_env_set_self_collision(tg_env* env, int on) {
+  TG_CHECK_ARG(env != nullptr, "tg_env_set_self_collision: env is NULL");
+  env->flags = on ? (env->flags | TG_FLAG_SELF) : (env->flags & ~TG_FLAG_SELF);
+  return TG_OK;
 }
 
 // Test hook: use only the first `items` entries of the ambiguous queue (0 = all), so that the overflow path
@@ -642,8 +700,12 @@ int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int6
       }
       env->launches += 1;
     }
+    if (env->flags & TG_FLAG_SELF) {
+      k_self_configs<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(arm + 8 * off, nb, valid + off);
+      env->launches += 1;
+    }
     if (clearance) {
-      k_clearance<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(env->grid, ex, arm + 8 * off, base + 3 * off, nb, clearance + off);
+      k_clearance<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(env->grid, ex, arm + 8 * off, base + 3 * off, nb, clearance + off, env->flags);
       env->launches += 1;
     }
   }
@@ -684,6 +746,11 @@ int tg_check_edges_slot(tg_env* env, const float* arm0, const float* base0, cons
     env->launches += 1;
     if (!env->grid.empty) {
       k_resolve<<<env->sm_count * env->occ_resolve, TGR_BLOCK, 0, st>>>(env->grid, qu, valid + off, env->counters_dev);
+      env->launches += 1;
+    }
+    if (env->flags & TG_FLAG_SELF) {
+      k_self_edges<<<tg_div_up(ne, TG_BLOCK / 32), TG_BLOCK, 0, st>>>(arm0 + 8 * off, base0 + 3 * off, arm1 + 8 * off, base1 + 3 * off, ne, rake,
+                                                                    resolution, valid + off);
       env->launches += 1;
     }
   }

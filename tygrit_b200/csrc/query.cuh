@@ -15,6 +15,15 @@
 #include "common.cuh"
 #include "fk.cuh"
 
+#ifdef TG_STATS
+__device__ unsigned long long tg_stats[16];
+#define TG_STAT(i, v) do { if ((threadIdx.x & 31) == 0) atomicAdd(&tg_stats[i], (unsigned long long)(v)); } while (0)
+#define TG_STAT_LANE(i, v) atomicAdd(&tg_stats[i], (unsigned long long)(v))  // the caller picks the lane
+#else
+#define TG_STAT(i, v) do { } while (0)
+#define TG_STAT_LANE(i, v) do { } while (0)
+#endif
+
 // Distance code of the voxel containing (gx, gy, gz) (voxel units).  Adding the 2^23 bias rounds to the
 // nearest voxel in the mantissa; subtracting the bit pattern of 2^23 as an unsigned and taking the
 // unsigned minimum with n - 1 clamps both sides at once — one DPX add-min per axis — because values
@@ -22,6 +31,7 @@
 // one, which is equivalent: every boundary voxel is at least W voxels from the cloud (tg_plan_grids pads
 // the box by W + 3), so both read "free".
 __device__ __forceinline__ int tg_probe(const TgGrid& g, float gx, float gy, float gz) {
+  TG_STAT_LANE(10, 1);  // executed probes (one per lane)
 #ifndef TG_LINEAR_PROBE
   // texture path: point sampling floors (g - m + 0.5) = the nearest voxel, clamp addressing keeps probes outside the
   // grid on a boundary voxel (which reads "free": the box is padded by W + 3 voxels), block-linear array layout
@@ -42,6 +52,9 @@ __device__ __forceinline__ int tg_probe(const TgGrid& g, float gx, float gy, flo
 // straight-line code so the texture handle stays in a uniform register (a tex3D under a divergent branch makes the
 // compiler wrap every fetch in a handle-uniformity loop).
 __device__ __forceinline__ int tg_probe_if(const TgGrid& g, bool need, float gx, float gy, float gz, int skipped) {
+#ifdef TG_STATS
+  atomicAdd(&tg_stats[need ? 10 : 11], 1ull);  // executed / skipped (derived bound) probes
+#endif
 #ifndef TG_LINEAR_PROBE
   unsigned c;
   asm("{\n\t.reg .pred p;\n\t.reg .u32 t1, t2, t3;\n\tsetp.ne.s32 p, %5, 0;\n\tmov.u32 %0, %6;\n\t"
@@ -347,14 +360,6 @@ __device__ inline float tg_sphere_clearance(const TgGrid& g, float cx, float cy,
 // ranges of the 32 rows are then concatenated (warp prefix sum) and scanned together, 32 points per
 // step with coalesced float4 loads; the first hit ends the walk through __any_sync.
 // ------------------------------------------------------------------------------------------------
-#ifdef TG_STATS
-__device__ unsigned long long tg_stats[16];
-#define TG_STAT(i, v) do { if ((threadIdx.x & 31) == 0) atomicAdd(&tg_stats[i], (unsigned long long)(v)); } while (0)
-#define TG_STAT_LANE(i, v) atomicAdd(&tg_stats[i], (unsigned long long)(v))  // the caller picks the lane
-#else
-#define TG_STAT(i, v) do { } while (0)
-#define TG_STAT_LANE(i, v) do { } while (0)
-#endif
 
 struct TgRows {  // cell rows of a sphere's bounding box
   int z0, y0, ny, nrows;
@@ -513,6 +518,62 @@ __device__ __forceinline__ float4 tg_sphere_world(const TgFrame* L, const TgBase
   const float3 pw = tg_to_world(b, pb.x, pb.y, pb.z);
   return make_float4(pw.x, pw.y, pw.z, l.w);
 }
+
+// Optional self-collision term (flag TG_FLAG_SELF, off by default): sphere-vs-sphere between the link pairs of the
+// reference's SELF_COLLISION_PAIRS (TyGrit/rl/train.py:78-107; VAMP's own pair list is unavailable).  Evaluated in the
+// base_link frame (the base pose cancels), head = 0.  Link pairs whose enclosing spheres are apart are pruned, then
+// sphere i of link a is tested against link b's enclosing sphere before its spheres.  Returns
+// min(|c_i - c_j| - r_i - r_j) over the tested pairs, clipped from above at `stop_above` pruning (pairs that cannot
+// come below it are skipped); with stop_at_hit the walk ends at the first touching pair (returns <= 0).
+static __device__ __noinline__ float tg_self_clearance(const float* q8, float stop_above, bool stop_at_hit) {
+  float q10[10];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) q10[i] = q8[i];
+  q10[8] = q10[9] = 0.f;
+  TgFrame L[TGM_N_LINKS];
+  tg_fk_links(q10, L);
+  float best = stop_above;
+  for (int a = 0; a < TGM_N_LINKS; ++a) {
+    const unsigned partners = TGM_SELF_PARTNERS[a];
+    const int na = TGM_LINK_SPH_COUNT[a];
+    if (partners == 0u || na == 0) continue;
+    const float4 ba = TGM_LINK_BOUND[a];
+    const float3 ca = tg_frame_apply(L[a], ba.x, ba.y, ba.z);
+    for (int b = 0; b < TGM_N_LINKS; ++b) {
+      const int nb = TGM_LINK_SPH_COUNT[b];
+      if (!((partners >> b) & 1u) || nb == 0) continue;
+      const float4 bb = TGM_LINK_BOUND[b];
+      const float3 cb = tg_frame_apply(L[b], bb.x, bb.y, bb.z);
+      {
+        const float dx = ca.x - cb.x, dy = ca.y - cb.y, dz = ca.z - cb.z;
+        const float reach = ba.w + bb.w + fmaxf(best, 0.f);
+        if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) > reach * reach) continue;
+      }
+      for (int i = 0; i < na; ++i) {
+        const float4 si = TGM_SPH_REF[TGM_LINK_SPH_FIRST[a] + i];
+        const float3 ci = tg_frame_apply(L[a], si.x, si.y, si.z);
+        {
+          const float dx = ci.x - cb.x, dy = ci.y - cb.y, dz = ci.z - cb.z;
+          const float reach = si.w + bb.w + fmaxf(best, 0.f);
+          if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) > reach * reach) continue;
+        }
+        for (int j = 0; j < nb; ++j) {
+          const float4 sj = TGM_SPH_REF[TGM_LINK_SPH_FIRST[b] + j];
+          const float3 cj = tg_frame_apply(L[b], sj.x, sj.y, sj.z);
+          const float dx = ci.x - cj.x, dy = ci.y - cj.y, dz = ci.z - cj.z;
+          const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz)), rr = si.w + sj.w;
+          if (stop_at_hit) {
+            if (d2 <= rr * rr) return -1.f;
+          } else {
+            best = fminf(best, sqrtf(d2) - rr);
+          }
+        }
+      }
+    }
+  }
+  return best;
+}
+__device__ __forceinline__ bool tg_self_hit(const float* q8) { return tg_self_clearance(q8, 0.f, true) < 0.f; }
 
 // Sphere obstacles and end-effector attachment (vamp_preview.py:242-304), brute force, exact.
 static __device__ __noinline__ bool tg_extras_hit(const TgGrid& g, const TgExtras& ex, const float* cfg /*x,y,th,q0..q7*/) {

@@ -121,6 +121,10 @@ class CollisionWorld:
             "tg_env_set_attachment",
         )
 
+    def set_self_collision(self, on: bool) -> None:
+        """Optional sphere-vs-sphere term over the reference's SELF_COLLISION_PAIRS (rl/train.py:78-107); off by default."""
+        N.check(self._lib.tg_env_set_self_collision(self._h, int(bool(on))), "tg_env_set_self_collision")
+
     def stats(self) -> dict[str, float]:
         out = (C.c_double * 8)()
         N.check(self._lib.tg_env_stats(self._h, out), "tg_env_stats")

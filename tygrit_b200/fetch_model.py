@@ -116,6 +116,16 @@ SPHERE_LINK = SPHERES[:, 0].astype(np.int64)
 SPHERE_XYZR = SPHERES[:, 1:5]
 
 
+# Non-adjacent link pairs that can physically self-collide (reference list: TyGrit/rl/train.py:78-107,
+# SELF_COLLISION_PAIRS).  head_tilt_link has no spheres, so its pairs add no sphere-sphere test.
+_DISTAL = ("wrist_flex_link", "wrist_roll_link", "gripper_link", "l_gripper_finger_link", "r_gripper_finger_link")
+_ARM_FROM_UPPERARM = ("upperarm_roll_link", "elbow_flex_link", "forearm_roll_link") + _DISTAL
+SELF_COLLISION_PAIRS = tuple(
+    [("head_pan_link", b) for b in _ARM_FROM_UPPERARM] + [("head_tilt_link", b) for b in _ARM_FROM_UPPERARM]
+    + [("base_link", b) for b in _DISTAL] + [("torso_lift_link", b) for b in _DISTAL]
+)
+
+
 def fetch_spheres_dict() -> dict[str, list[list[float]]]:
     """The table in the reference's ``FETCH_SPHERES`` shape (link -> [[x,y,z,r], ...])."""
     out: dict[str, list[list[float]]] = {}

@@ -156,3 +156,54 @@ def random_states(n: int, seed: int = 42, base_box=(-3.0, 3.0, -2.0, 2.0)) -> np
 
 
 HEAD_CAMERA_K = np.array([[154.10223, 0.0, 320.0], [0.0, 154.10223, 240.0], [0.0, 0.0, 1.0]])
+
+
+# --------------------------------------------------------------------------- #
+# device-side generators (bench.py: 64 Mi configurations never cross PCIe)
+# --------------------------------------------------------------------------- #
+TUCK_ARM = (0.0, 1.32, 1.40, -0.2, 1.72, 0.0, 1.66, 0.0)   # the reference tests' tuck configuration (test/test_planner.py:35)
+
+
+def device_configs(n: int, seed: int, device, base_box=(-3.5, 3.5, -2.5, 2.5)):
+    """arm (n,8), base (n,3) f32 CUDA tensors: the distribution of :func:`random_configs`, torch Philox stream."""
+    import torch
+
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    lo = torch.tensor(JOINT_LOWER, dtype=torch.float32, device=device)
+    hi = torch.tensor(JOINT_UPPER, dtype=torch.float32, device=device)
+    arm = torch.rand(n, 8, generator=gen, device=device) * (hi - lo) + lo
+    blo = torch.tensor([base_box[0], base_box[2], -np.pi], dtype=torch.float32, device=device)
+    bhi = torch.tensor([base_box[1], base_box[3], np.pi], dtype=torch.float32, device=device)
+    base = torch.rand(n, 3, generator=gen, device=device) * (bhi - blo) + blo
+    return arm, base
+
+
+def free_base_configs(world, n: int, seed: int, device, base_box=(-3.5, 3.5, -2.5, 2.5), chunk: int = 1 << 24):
+    """Planner-like ("free-heavy") batch: the base is drawn uniformly from the floor positions at which the robot with
+    its arm TUCKED is collision-free in ``world`` (rejection sampling with the engine itself), the arm uniformly from
+    the joint limits.  Returns (arm, base, accepted fraction of the floor)."""
+    import torch
+
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed + 7919)
+    blo = torch.tensor([base_box[0], base_box[2], -np.pi], dtype=torch.float32, device=device)
+    bhi = torch.tensor([base_box[1], base_box[3], np.pi], dtype=torch.float32, device=device)
+    tuck = torch.tensor(TUCK_ARM, dtype=torch.float32, device=device)
+    out, have, tried, kept = [], 0, 0, 0
+    while have < n:
+        m = int(min(chunk, max(4096, 3 * (n - have))))
+        cand = torch.rand(m, 3, generator=gen, device=device) * (bhi - blo) + blo
+        ok = world.check_configs(tuck.expand(m, 8).contiguous(), cand).bool()
+        good = cand[ok]
+        tried, kept = tried + m, kept + int(good.shape[0])
+        if kept == 0 and tried >= 4 * chunk:
+            raise RuntimeError("free_base_configs: no free floor position found")
+        good = good[: n - have]
+        out.append(good)
+        have += int(good.shape[0])
+    base = torch.cat(out).contiguous()
+    lo = torch.tensor(JOINT_LOWER, dtype=torch.float32, device=device)
+    hi = torch.tensor(JOINT_UPPER, dtype=torch.float32, device=device)
+    arm = torch.rand(n, 8, generator=gen, device=device) * (hi - lo) + lo
+    return arm, base, kept / max(tried, 1)

@@ -66,6 +66,31 @@ class PlanResult:
     stats: dict[str, float] = field(default_factory=dict)
 
 
+def tygrit_types() -> dict[str, Any] | None:
+    """TyGrit's own value types when the package is importable (a deployment inside TyGrit), else None."""
+    try:
+        from TyGrit.types.failures import PlannerFailure as _PF
+        from TyGrit.types.geometry import SE2Pose as _SE2
+        from TyGrit.types.planning import Trajectory as _TR
+        from TyGrit.types.results import PlanResult as _PR
+        from TyGrit.types.robot import RobotState as _RS, WholeBodyConfig as _WB
+        from TyGrit.types.sensor import SensorSnapshot as _SS
+    except Exception:
+        return None
+    return {"SE2Pose": _SE2, "WholeBodyConfig": _WB, "RobotState": _RS, "SensorSnapshot": _SS, "Trajectory": _TR,
+            "PlannerFailure": _PF, "PlanResult": _PR}
+
+
+# Inside TyGrit the planner returns TyGrit's own PlanResult / PlannerFailure / Trajectory, so enum identity and
+# isinstance checks of existing callers survive; standalone, the structural twins above are used.
+_TWINS = {"SE2Pose": SE2Pose, "WholeBodyConfig": WholeBodyConfig, "RobotState": RobotState, "SensorSnapshot": SensorSnapshot,
+          "Trajectory": Trajectory, "PlannerFailure": PlannerFailure, "PlanResult": PlanResult}
+_ext = tygrit_types()
+USING_TYGRIT_TYPES = _ext is not None
+if _ext is not None:
+    globals().update(_ext)
+
+
 def base_xyt(pose: Any) -> tuple[float, float, float]:
     """``(x, y, theta)`` of anything pose-like (SE2Pose, TyGrit SE2Pose, 3-sequence)."""
     if hasattr(pose, "theta"):

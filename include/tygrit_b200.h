@@ -106,6 +106,12 @@ int tg_env_blob_ptr(tg_env* env, void** blob);
  * voxels_per_metre actually used, slack [m].                                    */
 int tg_env_stats(const tg_env* env, double* out8);
 
+/* Layout of the built structure (HOST out, 20 doubles): [0] empty flag, [1..3] distance-grid nx, ny, nz, [4..6] index bias
+ * per axis (voxel index = round(p * vpm + bias) - 2^23), [7] voxels per metre, [8] metres per code, [9] slack, [10] window
+ * in voxels, [11] byte offset of the distance grid in the blob, [12] byte offset of the coarse far-field grid,
+ * [13..15] its dims, [16] voxels per coarse block edge, [17] metres per coarse code.  For tests and tools.          */
+int tg_env_grid_info(const tg_env* env, double* out20);
+
 /* ---- forward kinematics (fk_numpy.py:32-157, fk_torch.py:119-283) ------------- */
 /* World centres of the 111 spheres in the reference's sphere order; head2 may be
  * NULL (= 0, 0: the planner's model).  arm B x 8, base B x 3, head2 B x 2,
@@ -155,6 +161,10 @@ int tg_debug_stats(int64_t* out16, int reset);
  * events on the launching stream.  tg_env_timing_read waits for them and returns
  * {phase-1 ms, phase-2 ms, launch pairs} accumulated since the last read (HOST out, 3 doubles). */
 int tg_env_set_timing(tg_env* env, int on);
+/* Test / tuning hook: the configuration kernel proves most spheres of a free configuration free from a coarse far-field
+ * distance grid held in shared memory (used from 2^18 configurations per launch).  0 switches that variant off; the
+ * verdicts do not depend on it.                                                                                    */
+int tg_env_set_coarse(tg_env* env, int on);
 /* Test hook: use only the first `items` entries of the ambiguous queue (0 = all) so that the
  * overflow path (items resolved inline by their own lane) can be exercised with small batches. */
 int tg_env_set_queue_limit(tg_env* env, int64_t items);

@@ -244,19 +244,16 @@ def test_host_api_matches_device_api_and_chunks(room):
 
 
 def _read_structure(w):
-    """Parse the structure blob header (csrc/common.cuh TgHeader/TgGrid) and return the df code grid."""
-    import struct
-
-    n = w.used_bytes()
-    blob = w.blob_view(n).cpu().numpy()
-    magic, used, off_df, off_cells, off_pts = struct.unpack_from("<5Q", blob, 0)
-    vpm, b0, b1, b2, h0, h1, h2 = struct.unpack_from("<7f", blob, 40)
-    nx, ny, nz, nxy = struct.unpack_from("<4i", blob, 68)
-    idx_bias, = struct.unpack_from("<I", blob, 84)
-    q, slack = struct.unpack_from("<2f", blob, 88)
-    window, = struct.unpack_from("<i", blob, 96)
+    """Read the distance grid and the coarse far-field grid back from the structure blob (tg_env_grid_info gives the layout)."""
+    gi = w.grid_info()
+    blob = w.blob_view(w.used_bytes()).cpu().numpy()
+    nx, ny, nz = int(gi["nx"]), int(gi["ny"]), int(gi["nz"])
+    gnx, gny, gnz = int(gi["gnx"]), int(gi["gny"]), int(gi["gnz"])
+    off_df, off_cg = int(gi["off_df"]), int(gi["off_cg"])
     df = blob[off_df:off_df + nx * ny * nz].reshape(nz, ny, nx)
-    return dict(vpm=np.float32(vpm), bias=np.array([b0, b1, b2], np.float32), n=(nx, ny, nz), q=q, slack=slack, W=window, df=df)
+    cg = blob[off_cg:off_cg + gnx * gny * gnz].reshape(gnz, gny, gnx)
+    return dict(vpm=np.float32(gi["voxels_per_metre"]), bias=np.array([gi["bias_x"], gi["bias_y"], gi["bias_z"]], np.float32), n=(nx, ny, nz),
+                q=gi["q"], slack=gi["slack"], W=int(gi["window"]), df=df, cg=cg, cg_r=int(gi["cg_r"]), cg_q=gi["cg_q"])
 
 
 @pytest.mark.parametrize("vpm", [50.0, 80.0])
@@ -289,6 +286,19 @@ def test_distance_grid_codes_bit_exact_vs_scipy_edt(vpm):
     got = st["df"]
     bad = np.argwhere(got != want)
     assert bad.shape[0] == 0, f"{bad.shape[0]} voxel codes differ, first {bad[:3]}: got {got[tuple(bad[0])]} want {want[tuple(bad[0])]}"
+    # coarse far-field grid: every code must be a LOWER bound (in units of cg_q) on the distance from ANY point of its
+    # block of cg_r^3 voxels to the cloud, and not uselessly loose.  Exact reference: distance of the voxel centres to the
+    # points' voxel centres (scipy) minus the two half-diagonals a point and a query can sit off their voxel centres.
+    r, cq, cg = st["cg_r"], st["cg_q"], st["cg"]
+    assert cg.shape == (-(-nz // r), -(-ny // r), -(-nx // r)) and cg.size <= 180224
+    d = ndimage.distance_transform_edt(~occ) / np.float64(st["vpm"])
+    pad = [(0, cg.shape[a] * r - d.shape[a]) for a in range(3)]
+    dmin = np.pad(d, pad, constant_values=np.inf).reshape(cg.shape[0], r, cg.shape[1], r, cg.shape[2], r).min(axis=(1, 3, 5))
+    true_lo = dmin - np.sqrt(3.0) / np.float64(st["vpm"])          # any point of a voxel vs any point of an occupied voxel
+    claimed = cg.astype(np.float64) * cq
+    assert (claimed <= np.maximum(true_lo, 0.0) + 1e-6).all(), "a coarse code claims more clearance than there is"
+    far = dmin > 3.5 * r / np.float64(st["vpm"])
+    assert far.any() and (claimed[far] >= np.minimum(dmin[far], 1.0) - 2.0 * np.sqrt(3.0) * r / np.float64(st["vpm"]) - 2 * cq).all()
     w.close()
 
 
@@ -558,6 +568,30 @@ def test_bench_configuration_500k_72vpm_vs_fp64_oracle(bench_world):
     ev = w.check_edges(_cuda(a0), _cuda(b0), _cuda(a1), _cuda(b1)).cpu().numpy()
     ecl, _ = cc.edge_clearance(a0, b0, a1, b1, cap=1e-3)
     _assert_verdicts(ev, ecl, "bench-world edges")
+
+
+def test_coarse_far_field_variant_gives_identical_verdicts(bench_world, tabletop):
+    """Batches of >= 2^18 configurations run the variant of the configuration kernel that holds the coarse far-field grid
+    in shared memory (most spheres of a free configuration are proven free without touching the fine grid).  Its verdicts
+    and its ambiguous-item counts must be those of the plain variant, on a large world and on a small one."""
+    dev = torch.device("cuda", 0)
+    for (cloud, w, cc), box in ((bench_world, (-3.5, 3.5, -2.5, 2.5)), (tabletop, (-1.5, 2.5, -2.0, 2.0))):
+        arm, base = synth.device_configs(400_000, seed=77, device=dev, base_box=box)
+        f_arm, f_base, _ = synth.free_base_configs(w, 300_000, seed=78, device=dev, base_box=box)
+        for a, b in ((arm, base), (f_arm, f_base)):
+            w.counters()
+            with_coarse = w.check_configs(a, b)
+            c1 = w.counters()
+            try:
+                w.set_coarse(False)
+                plain = w.check_configs(a, b)
+                c0 = w.counters()
+            finally:
+                w.set_coarse(True)
+            assert torch.equal(with_coarse, plain)
+            assert c1["narrow_items"] <= c0["narrow_items"] and c1["definite_collisions"] == c0["definite_collisions"]
+            _assert_verdicts(with_coarse[:100_000].cpu().numpy(), cc.clearance(a[:100_000].cpu().numpy(), b[:100_000].cpu().numpy(), cap=1e-3),
+                             "coarse variant")
 
 
 def test_self_collision_term_vs_oracle(tabletop):

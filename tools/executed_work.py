@@ -49,7 +49,7 @@ s = [int(v) for v in out]
 B = a.configs
 print(json.dumps({
     "configs": B, "voxels_per_metre": a.vpm, "workload": a.workload, "free_fraction": float(valid.float().mean().item()),
-    "probes_per_config": s[10] / B, "stage_b_fraction": s[12] / B, "probes_skipped_by_derived_bound_per_config": s[11] / B,
+    "coarse_lookups_per_config": s[13] / B, "probes_per_config": s[10] / B, "stage_b_fraction": s[12] / B, "probes_skipped_by_derived_bound_per_config": s[11] / B,
     "narrow_items_per_config": cnt["narrow_items"] / B, "definite_collision_fraction": cnt["definite_collisions"] / B,
     "narrow_spheres_listed_per_config": s[1] / B, "narrow_spheres_walked_per_config": s[2] / B,
     "narrow_point_tests_per_config": s[9] / B, "narrow_row_batches_per_config": s[3] / B,

@@ -36,8 +36,10 @@ _SIGS = {
     "tg_env_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "tg_env_blob_capacity": (C.c_size_t, [C.c_void_p]),
     "tg_env_blob_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "tg_env_grid_info": (C.c_int, [C.c_void_p, C.c_void_p]),
     "tg_env_stats": (C.c_int, [C.c_void_p, C.c_void_p]),
     "tg_env_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "tg_env_set_coarse": (C.c_int, [C.c_void_p, C.c_int]),
     "tg_env_set_queue_limit": (C.c_int, [C.c_void_p, C.c_int64]),
     "tg_env_timing_read": (C.c_int, [C.c_void_p, C.c_void_p]),
     "tg_env_counters": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),

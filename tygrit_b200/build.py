@@ -92,10 +92,9 @@ def build_oracle(force: bool = False) -> str | None:
 
 if __name__ == "__main__":
     print(build_cuda(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_cuda(force="--force" in sys.argv, stats=True))  # the counting build must never lag behind the product library
     if "--variant" in sys.argv:  # tuning aid: python -m tygrit_b200.build --variant NAME -DFOO=1 ... -> lib/libtygrit_b200_NAME.so
         i = sys.argv.index("--variant")
         name, flags = sys.argv[i + 1], [a for a in sys.argv[i + 2:] if a.startswith("-D")]
         print(_build(os.path.join(LIBDIR, f"libtygrit_b200_{name}.so"), os.path.join(LIBDIR, name), flags, True, False))
-    if "--stats" in sys.argv:
-        print(build_cuda(force="--force" in sys.argv, stats=True))
     print(build_oracle(force="--force" in sys.argv))

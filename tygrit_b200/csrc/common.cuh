@@ -22,6 +22,7 @@
 #define TG_CLEARANCE_CAP 0.25f
 #define TG_FLAG_SELF 1  // tg_env.flags: self-collision term on (tg_env_set_self_collision)
 #define TG_HOST_MAX_CHUNKS 4096
+#define TG_COARSE_MAX 180224  // bytes of the coarse far-field grid: it lives in SHARED memory of the phase-1 kernel (176 KB)
 #define TG_HOST_SMALL 16384  // host batches up to this size go through one packed H2D copy and one D2H copy
 
 struct TgGrid {
@@ -50,6 +51,13 @@ struct TgGrid {
   float tex_bias[3];          // voxel coordinate -> texel coordinate: 0.5 - m
   const uint32_t* cell_start;
   const float4* pts;
+  // coarse far-field grid (one byte per block of cg_r^3 voxels): code c means dist(x, cloud) >= c * cg_q for every x of the
+  // block.  Small enough (<= TG_COARSE_MAX bytes) to be copied into shared memory by every CTA of the phase-1 kernel.
+  const uint8_t* cg;
+  int gnx, gny, gnz;    // coarse dims = ceil(n / cg_r)
+  int cg_r;             // voxels per coarse block edge
+  float cg_inv_r;       // 1 / cg_r
+  float cg_q;           // metres per coarse code unit
 };
 
 // per-sphere integer thresholds on the df code (kernel order): definitely free iff code >= free_ge,
@@ -59,6 +67,8 @@ struct TgThr {
   int coll_le[TG_N_SPHERES];
   int bound_ge[16];  // per cull group (fetch_model.cuh TGM_BOUND): enclosing sphere definitely free iff code >= bound_ge
   int src_ge[TG_N_SPHERES];  // derived bound: sphere definitely free iff the code at its source point (tgm_k_src) >= src_ge
+  int cfree_ge[TG_N_SPHERES];  // coarse far-field code at the sphere centre >= cfree_ge: definitely free (no fine probe needed)
+  int cbound_ge[16];           // same for the enclosing sphere of a cull group
 };
 
 struct TgExtras {  // sphere obstacles + end-effector attachment (rarely used; brute force)
@@ -71,7 +81,7 @@ struct TgExtras {  // sphere obstacles + end-effector attachment (rarely used; b
 struct TgHeader {  // first TG_HEADER_BYTES of the blob
   uint64_t magic;
   uint64_t bytes;  // used bytes of the blob
-  uint64_t off_df, off_cells, off_pts;
+  uint64_t off_df, off_cells, off_pts, off_cg;
   TgGrid grid;     // pointers are rebased on import
   TgThr thr;
 };
@@ -135,6 +145,8 @@ struct tg_env {
   cudaArray_t df_array;       // block-linear copy of the distance grid, read through the texture path by phase 1
   cudaTextureObject_t df_tex;
   int arr_n[3];
+  uint32_t* cbits;       // coarse occupancy bitmask [gnz][gny][ceil(gnx/32)]
+  uint32_t* g2c;         // coarse EDT intermediate, u16 pairs
   uint8_t* g1;           // EDT pass X output, u8 [nvox]
   uint16_t* g2;          // EDT pass Y output, u16 [nvox]
   uint32_t* cell_count;  // [max_cells + 1]
@@ -155,6 +167,7 @@ struct tg_env {
   unsigned queue_capacity;
   unsigned queue_limit;  // test hook: 0 = use the whole queue
   int flags;             // TG_FLAG_*: optional terms evaluated by their own kernels after the cloud verdicts
+  int no_coarse;         // 1 = never use the coarse far-field variant of the configuration kernel (test / tuning hook)
   TgCounters* counters_dev;
   TgCounters* counters_host;  // pinned
   int64_t launches;

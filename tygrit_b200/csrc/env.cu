@@ -82,8 +82,8 @@ __global__ void __launch_bounds__(256) k_bounds(const float* __restrict__ xyz, i
 // per point: cell key + rank in cell; mark the df voxel.  Points that are not finite or fall
 // outside the grids are dropped (key = 0xFFFFFFFF) and counted.
 __global__ void __launch_bounds__(256)
-k_count(const float* __restrict__ xyz, int n, TgGrid g, uint32_t* __restrict__ occ_bits, int nwx, uint32_t* __restrict__ cell_count,
-        uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int* __restrict__ dropped) {
+k_count(const float* __restrict__ xyz, int n, TgGrid g, uint32_t* __restrict__ occ_bits, int nwx, uint32_t* __restrict__ cbits, int cnwx,
+        uint32_t* __restrict__ cell_count, uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int* __restrict__ dropped) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
@@ -100,6 +100,8 @@ k_count(const float* __restrict__ xyz, int n, TgGrid g, uint32_t* __restrict__ o
       const unsigned ix = __float_as_uint(fx) - TG_MAGIC_BITS, iy = __float_as_uint(fy) - TG_MAGIC_BITS,
                      iz = __float_as_uint(fz) - TG_MAGIC_BITS;
       atomicOr(&occ_bits[((size_t)iz * g.ny + iy) * nwx + (ix >> 5)], 1u << (ix & 31));
+      const unsigned jx = ix / (unsigned)g.cg_r, jy = iy / (unsigned)g.cg_r, jz = iz / (unsigned)g.cg_r;
+      atomicOr(&cbits[(jz * g.gny + jy) * cnwx + (jx >> 5)], 1u << (jx & 31));
       k = (uint32_t)((cz * g.cny + cy) * g.cnx + cx);
       rank[i] = atomicAdd(&cell_count[k], 1u);
     }
@@ -312,6 +314,59 @@ k_edt_z(const uint32_t* __restrict__ g2w, uint8_t* __restrict__ df, int nx, int 
   }
 }
 
+// pass Z of the COARSE far-field grid: the same transform on blocks of cg_r^3 voxels (a block is occupied when any of
+// its voxels is); the output code is a LOWER bound in units of cq metres on the distance from ANY point of the block to
+// the cloud:  lo = |centre - nearest occupied block centre| - 2 * (half diagonal of a block)  (both points can sit
+// anywhere in their blocks), floored.  Nothing within W blocks: lo from W.
+template <int WB>
+__global__ void __launch_bounds__(TGE_THREADS)
+k_edt_z_coarse(const uint32_t* __restrict__ g2w, uint8_t* __restrict__ cg, int nx, int nxp, int ny, int nz, int W, float cell, float cq) {
+  extern __shared__ uint32_t tile[];
+  __shared__ uint8_t lut[1024];
+  __shared__ uint8_t sat;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int x = blockIdx.x * 64 + 2 * lane, y = blockIdx.y, z0 = blockIdx.z * TGE_SEG;
+  const float two_h = 1.7320509f * cell + 3e-5f;
+  for (int d2 = threadIdx.x; d2 <= 1024; d2 += TGE_THREADS) {
+    const float d = d2 < W * W ? sqrtf((float)d2) : (float)W;
+    const uint8_t c = (uint8_t)min(255, max(0, (int)floorf((d * cell * 0.999999f - two_h) / cq)));
+    if (d2 < 1024) lut[d2] = c;
+    if (d2 == 1024) sat = c;
+  }
+  for (int r = warp; r < TGE_SEG + 2 * WB; r += TGE_THREADS / 32) {
+    const int z = z0 - WB + r;
+    unsigned v = TGE_SENT2;
+    if (z >= 0 && z < nz && x < nxp) v = __ldg(g2w + ((((size_t)z * ny + y) * nxp + x) >> 1));
+    tile[r * 32 + lane] = v;
+  }
+  __syncthreads();
+  if (x >= nx) return;
+  for (int r0 = TGE_T * warp; r0 < TGE_SEG; r0 += TGE_T * (TGE_THREADS / 32)) {
+    if (z0 + r0 >= nz) break;
+    unsigned best[TGE_T];
+    tge_taps_blocked<WB>(tile + (WB + r0) * 32 + lane, best);
+#pragma unroll
+    for (int t = 0; t < TGE_T; ++t) {
+      const int z = z0 + r0 + t;
+      if (z < nz) {
+        const unsigned lo = best[t] & 0xFFFFu, hi = best[t] >> 16;
+        uint8_t* out = cg + ((size_t)z * ny + y) * nx + x;
+        out[0] = lo < 1024u ? lut[lo] : sat;
+        if (x + 1 < nx) out[1] = hi < 1024u ? lut[hi] : sat;
+      }
+    }
+  }
+}
+
+template <int WB>
+static void tg_launch_edt_coarse(const uint32_t* cbits, uint32_t* g2c, uint8_t* cg, const TgGrid& g, int W, float cell, cudaStream_t st) {
+  const int nxp = (g.gnx + 1) & ~1, nwx = (g.gnx + 31) / 32;
+  const size_t tile_bytes = (size_t)(TGE_SEG + 2 * WB) * 32 * sizeof(uint32_t);
+  k_edt_xy<WB><<<dim3(tg_div_up(nxp, 64), tg_div_up(g.gny, TGE_SEG), g.gnz), TGE_THREADS, tile_bytes, st>>>(cbits, g2c, g.gnx, nxp, nwx, g.gny, W);
+  k_edt_z_coarse<WB><<<dim3(tg_div_up(g.gnx, 64), g.gny, tg_div_up(g.gnz, TGE_SEG)), TGE_THREADS, tile_bytes, st>>>(g2c, cg, g.gnx, nxp, g.gny, g.gnz, W,
+                                                                                                               cell, g.cg_q);
+}
+
 template <int WB>
 static void tg_launch_edt(const uint32_t* occ_bits, uint32_t* g2, uint8_t* df, const TgGrid& g, int nxp, int nwx, cudaStream_t st) {
   const size_t tile_bytes = (size_t)(TGE_SEG + 2 * WB) * 32 * sizeof(uint32_t);
@@ -345,6 +400,11 @@ static void tg_compute_thresholds(const TgGrid& g, TgThr* thr) {
     const double R = (double)TGM_H_BOUND_RADIUS[b] + (double)g.r_pt;
     thr->bound_ge[b] = (int)floor((R + slack) / q) + 1;  // > 255: the window is too small to ever prove it
   }
+  for (int j = 0; j < TG_N_SPHERES; ++j)
+    thr->cfree_ge[j] = (int)floor(((double)TGM_H_RADIUS_K[j] + (double)g.r_pt + kEpsFp) / (double)g.cg_q) + 1;
+  for (int b = 0; b < 16; ++b) thr->cbound_ge[b] = 256;
+  for (int b = 0; b < TGM_N_BOUNDS; ++b)
+    thr->cbound_ge[b] = (int)floor(((double)TGM_H_BOUND_RADIUS[b] + (double)g.r_pt + kEpsFp) / (double)g.cg_q) + 1;
   // code c at the source point => no cloud point within c*q - slack of it; the sphere is inside the ball of radius
   // sep + r around the source (sep = centre separation in the rigid frame, rounded up in the generator)
   for (int j = 0; j < TG_N_SPHERES; ++j) {
@@ -391,6 +451,17 @@ static bool tg_plan_grids(tg_env* env, const float lo[3], const float hi[3], TgG
     g->nx = n[0]; g->ny = n[1]; g->nz = n[2];
     g->nxy = n[0] * n[1];
     g->idx_bias = TG_MAGIC_BITS * (1u + (unsigned)g->nx + (unsigned)g->nxy);
+    // coarse far-field grid: the smallest block edge (in voxels) whose grid fits TG_COARSE_MAX bytes
+    for (int r = 2; r <= 512; ++r) {
+      const long long cn = (long long)tg_div_up(n[0], r) * tg_div_up(n[1], r) * tg_div_up(n[2], r);
+      if (cn <= TG_COARSE_MAX) {
+        g->cg_r = r;
+        g->cg_inv_r = 1.0f / (float)r;
+        g->gnx = tg_div_up(n[0], r); g->gny = tg_div_up(n[1], r); g->gnz = tg_div_up(n[2], r);
+        break;
+      }
+    }
+    g->cg_q = 0.005f;
     break;
   }
   if (g->nx == 0) return false;
@@ -425,7 +496,9 @@ static void tg_layout(tg_env* env, TgGrid* g, TgHeader* h) {
   h->off_df = TG_HEADER_BYTES;
   h->off_cells = align256(h->off_df + nvox);
   h->off_pts = align256(h->off_cells + 4 * (ncell + 1));
-  h->bytes = align256(h->off_pts + 16 * (size_t)g->n_points);
+  h->off_cg = align256(h->off_pts + 16 * (size_t)g->n_points);
+  h->bytes = align256(h->off_cg + (size_t)g->gnx * g->gny * g->gnz);
+  g->cg = env->blob + h->off_cg;
   g->df = env->blob + h->off_df;
   g->cell_start = (const uint32_t*)(env->blob + h->off_cells);
   g->pts = (const float4*)(env->blob + h->off_pts);
@@ -496,9 +569,11 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
   env->cpmx_requested = 64.f;
   env->r_pt = point_radius;
   env->blob_capacity = TG_HEADER_BYTES + align256(env->max_voxels) + align256(4 * (env->max_cells + 1)) +
-                       align256(16 * (size_t)max_points) + 1024;
+                       align256(16 * (size_t)max_points) + align256(TG_COARSE_MAX) + 1024;
   TG_CUDA(cudaMalloc(&env->blob, env->blob_capacity));
   TG_CUDA(cudaMalloc(&env->g1, env->max_voxels));
+  TG_CUDA(cudaMalloc(&env->cbits, TG_COARSE_MAX / 8 + 4 * 4096));   // coarse occupancy bits (rows padded to words)
+  TG_CUDA(cudaMalloc(&env->g2c, 2 * TG_COARSE_MAX + 2 * 65536));    // u16 [gnz][gny][gnx rounded up to even]
   TG_CUDA(cudaMalloc(&env->g2, 2 * env->max_voxels + env->max_voxels / 8 + 4096));  // u16 [nz][ny][nxp], nxp = nx rounded up to even
   TG_CUDA(cudaMalloc(&env->cell_count, 4 * (env->max_cells + 1)));
   TG_CUDA(cudaMalloc(&env->rank, 4 * max_points));
@@ -532,6 +607,7 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
 extern "C" int tg_env_destroy(tg_env* env) {
   if (!env) return TG_OK;
   cudaSetDevice(env->device);
+  cudaFree(env->cbits); cudaFree(env->g2c);
   cudaFree(env->blob); cudaFree(env->g1); cudaFree(env->g2); cudaFree(env->cell_count);
   cudaFree(env->rank); cudaFree(env->key); cudaFree(env->scan_tmp); cudaFree(env->bounds_dev);
   cudaFree(env->xyz_stage); cudaFree(env->extras_dev); cudaFree(env->items); cudaFree(env->queue_count);
@@ -662,9 +738,12 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   const int nwx = (g.nx + 31) / 32, nxp = (g.nx + 1) & ~1;
   uint32_t* occ_bits = (uint32_t*)env->g1;  // occupancy bitmask [nz][ny][nwx]
   TG_CUDA(cudaMemsetAsync(occ_bits, 0, 4 * (size_t)g.nz * g.ny * nwx, st));
+  const int cnwx = (g.gnx + 31) / 32;
+  TG_CUDA(cudaMemsetAsync(env->cbits, 0, 4 * (size_t)g.gnz * g.gny * cnwx, st));
   TG_CUDA(cudaMemsetAsync(env->cell_count, 0, 4 * ((size_t)ncell + 1), st));
   TG_CUDA(cudaMemsetAsync(env->bounds_dev + 6, 0, sizeof(int), st));
-  k_count<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, g, occ_bits, nwx, env->cell_count, env->key, env->rank, env->bounds_dev + 6);
+  k_count<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, g, occ_bits, nwx, env->cbits, cnwx, env->cell_count, env->key, env->rank,
+                                             env->bounds_dev + 6);
   const int nb = tg_div_up(ncell, SCAN_ITEMS);
   k_scan_block_sums<<<nb, 256, 0, st>>>(env->cell_count, ncell, env->scan_tmp);
   k_scan_sums<<<1, 1024, 0, st>>>(env->scan_tmp, nb);
@@ -679,8 +758,22 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
     case 7: tg_launch_edt<28>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
     default: tg_launch_edt<32>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
   }
+  {  // coarse far-field grid: lower bounds out to ~1.2 m (255 codes of 5 mm)
+    const float cell = (float)g.cg_r / g.vpm;
+    const int Wc = min(31, (int)ceilf((255.0f * g.cg_q + 1.7320509f * cell) / cell) + 1);
+    uint8_t* cg = env->blob + h->off_cg;
+    switch ((Wc + 3) / 4) {
+      case 0: case 1: case 2: tg_launch_edt_coarse<8>(env->cbits, env->g2c, cg, g, Wc, cell, st); break;
+      case 3: tg_launch_edt_coarse<12>(env->cbits, env->g2c, cg, g, Wc, cell, st); break;
+      case 4: tg_launch_edt_coarse<16>(env->cbits, env->g2c, cg, g, Wc, cell, st); break;
+      case 5: tg_launch_edt_coarse<20>(env->cbits, env->g2c, cg, g, Wc, cell, st); break;
+      case 6: tg_launch_edt_coarse<24>(env->cbits, env->g2c, cg, g, Wc, cell, st); break;
+      case 7: tg_launch_edt_coarse<28>(env->cbits, env->g2c, cg, g, Wc, cell, st); break;
+      default: tg_launch_edt_coarse<32>(env->cbits, env->g2c, cg, g, Wc, cell, st); break;
+    }
+  }
   TG_CUDA(cudaGetLastError());
-  env->launches += 7;
+  env->launches += 9;
 
   tg_compute_thresholds(g, &env->thr);
   env->grid = g;
@@ -719,6 +812,22 @@ extern "C" int tg_env_stats(const tg_env* env, double* out8) {
     int dropped = 0;
     if (cudaMemcpy(&dropped, env->bounds_dev + 6, sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess) out8[1] = dropped;
   }
+  return TG_OK;
+}
+
+// Layout of the built structure inside the blob (for tests and tools that read the grids back).
+extern "C" int tg_env_grid_info(const tg_env* env, double* out20) {
+  TG_CHECK_ARG(env != nullptr && out20 != nullptr, "tg_env_grid_info: bad argument");
+  const TgGrid& g = env->grid;
+  const TgHeader* h = env->header_host;
+  for (int i = 0; i < 20; ++i) out20[i] = 0;
+  out20[0] = g.empty;
+  if (g.empty) return TG_OK;
+  out20[1] = g.nx; out20[2] = g.ny; out20[3] = g.nz;
+  for (int a = 0; a < 3; ++a) out20[4 + a] = g.bias[a];
+  out20[7] = g.vpm; out20[8] = g.q; out20[9] = g.slack; out20[10] = g.window;
+  out20[11] = (double)h->off_df; out20[12] = (double)h->off_cg;
+  out20[13] = g.gnx; out20[14] = g.gny; out20[15] = g.gnz; out20[16] = g.cg_r; out20[17] = g.cg_q;
   return TG_OK;
 }
 
@@ -762,6 +871,7 @@ extern "C" int tg_env_import(tg_env* env, const void* blob, size_t bytes, void* 
     g.df = env->blob + h->off_df;
     g.cell_start = (const uint32_t*)(env->blob + h->off_cells);
     g.pts = (const float4*)(env->blob + h->off_pts);
+    g.cg = env->blob + h->off_cg;
   }
   env->grid = g;
   env->thr = h->thr;

@@ -54,18 +54,25 @@ __device__ __forceinline__ void tg_push_item(const TgGrid& g, TgQueue qu, TgCoun
 // compacted through a shared-memory ring so that stage B (91 spheres + the arm chain) always runs
 // with full warps.  Two block barriers per tile of TGC_BLOCK configurations.
 // ------------------------------------------------------------------------------------------------
-#ifndef TGC_BLOCK
-#define TGC_BLOCK 512  // 2 blocks of 16 warps per SM: warps of a block run the same code region, which the instruction cache likes (A/B in profiles/)
+// Two instantiations: <1024, true> - ONE block of 32 warps per SM that first copies the coarse far-field grid
+// (<= 176 KB) into shared memory, so that most spheres of a free configuration are proven free by an LDS instead of an
+// L1-miss request to the L2-resident fine grid (the resource that bounds this kernel); <512, false> - two blocks per SM,
+// no coarse grid, for batches too small to amortise the copy.
+#define TGC_BLOCK_COARSE 1024
+#define TGC_BLOCK_PLAIN 512
+#ifndef TGC_COARSE_MIN_BATCH
+#define TGC_COARSE_MIN_BATCH (1 << 18)  // configurations per launch from which the coarse variant is used
 #endif
-#define TGC_RING (2 * TGC_BLOCK)  // >= 2 * TGC_BLOCK, power of two
 
-struct TgRing {
-  float cfg[11][TGC_RING];
-  uint32_t idx[TGC_RING];
-  uint32_t amb0[TGC_RING];
+template <int BLOCK>
+struct TgRing {  // survivors of stage A: base pose, index, ambiguous stage-A spheres (the arm is read by stage B)
+  float bx[2 * BLOCK], by[2 * BLOCK], bth[2 * BLOCK];
+  uint32_t idx[2 * BLOCK];
+  uint32_t amb0[2 * BLOCK];
 };
 
-__device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& thr, const TgExtras* __restrict__ ex,
+template <bool COARSE>
+__device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgExtras* __restrict__ ex,
                                                  const float* cfg, uint32_t idx, uint32_t amb0, uint8_t* __restrict__ valid,
                                                  TgQueue qu, TgCounters* ctr, bool live) {
   TgClass cl;
@@ -75,7 +82,7 @@ __device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& t
     TG_STAT_LANE(12, 1);  // configurations that reach stage B (arm FK executed)
     if (!g.empty) {
       const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
-      tg_stage_b<true>(g, thr, p, cfg + 3, cl);
+      tg_stage_b<true, COARSE>(g, thr, cg, p, cfg + 3, cl);
     }
     if (!cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
     valid[idx] = cl.collide ? 0 : 1;
@@ -86,24 +93,39 @@ __device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& t
   tg_push_item(g, qu, ctr, need, idx, cl.amb, cfg, valid);
 }
 
-__global__ void __launch_bounds__(TGC_BLOCK, 1024 / TGC_BLOCK)
+template <int BLOCK, bool COARSE>
+__global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
 k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm,
                 const float* __restrict__ base, int B, uint8_t* __restrict__ valid, TgQueue qu, TgCounters* ctr) {
+  constexpr unsigned RING = 2 * BLOCK;  // power of two
   extern __shared__ __align__(16) unsigned char tgc_smem[];
-  TgRing& ring = *reinterpret_cast<TgRing*>(tgc_smem);
+  TgRing<BLOCK>& ring = *reinterpret_cast<TgRing<BLOCK>*>(tgc_smem);
   __shared__ unsigned s_tail;
   if (threadIdx.x == 0) s_tail = 0;
+  TgCoarse cg;
+  if constexpr (COARSE) {
+    uint8_t* cgs = tgc_smem + sizeof(TgRing<BLOCK>);
+    if (!g.empty) {
+      const int n16 = (g.gnx * g.gny * g.gnz + 15) >> 4;  // the blob section is padded to 256 bytes
+      const uint4* src = reinterpret_cast<const uint4*>(g.cg);
+      uint4* dst = reinterpret_cast<uint4*>(cgs);
+      for (int i = threadIdx.x; i < n16; i += BLOCK) dst[i] = __ldg(src + i);
+    }
+    cg = tg_coarse_init(g, cgs);
+  } else {
+    cg = tg_coarse_init(g, nullptr);
+  }
   __syncthreads();
-  unsigned head = 0;  // ring positions count up; slot = position & (TGC_RING - 1)
+  unsigned head = 0;  // ring positions count up; slot = position & (RING - 1)
   const unsigned lane = threadIdx.x & 31;
-  const int ntiles = (B + TGC_BLOCK - 1) / TGC_BLOCK;
+  const int ntiles = (B + BLOCK - 1) / BLOCK;
   // The loop body holds the only copy of stage A and stage B (the kernel is instruction-cache
   // sensitive): the last, extra iteration (tile >= ntiles) only drains what is left in the ring.
   for (int tile = blockIdx.x;; tile += gridDim.x) {
     const bool last = tile >= ntiles;  // block-uniform
     float cfg[11];
     if (!last) {
-      const int i = tile * TGC_BLOCK + threadIdx.x;
+      const int i = tile * BLOCK + threadIdx.x;
       const bool live = i < B;
       TgClass cl;
       tg_class_clear(cl);
@@ -111,7 +133,7 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
         cfg[0] = __ldcs(base + 3 * (size_t)i); cfg[1] = __ldcs(base + 3 * (size_t)i + 1); cfg[2] = __ldcs(base + 3 * (size_t)i + 2);
         if (!g.empty) {
           const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
-          tg_stage_a(g, thr, p, cl);
+          tg_stage_a<COARSE>(g, thr, cg, p, cl);
         }
         if (cl.collide) valid[i] = 0;
       }
@@ -124,35 +146,37 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
         if (lane == 0) pos = atomicAdd(&s_tail, (unsigned)__popc(m));
         pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
         if (surv) {
-          const float4 a0 = __ldcs(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i);
-          const float4 a1 = __ldcs(reinterpret_cast<const float4*>(arm) + 2 * (size_t)i + 1);
-          const unsigned sl = pos & (TGC_RING - 1);
-          ring.cfg[0][sl] = cfg[0]; ring.cfg[1][sl] = cfg[1]; ring.cfg[2][sl] = cfg[2];
-          ring.cfg[3][sl] = a0.x; ring.cfg[4][sl] = a0.y; ring.cfg[5][sl] = a0.z; ring.cfg[6][sl] = a0.w;
-          ring.cfg[7][sl] = a1.x; ring.cfg[8][sl] = a1.y; ring.cfg[9][sl] = a1.z; ring.cfg[10][sl] = a1.w;
+          const unsigned sl = pos & (RING - 1);
+          ring.bx[sl] = cfg[0]; ring.by[sl] = cfg[1]; ring.bth[sl] = cfg[2];
           ring.idx[sl] = (uint32_t)i;
           ring.amb0[sl] = cl.amb[0];
         }
       }
     }
     __syncthreads();
-    const unsigned avail = s_tail - head;  // block-uniform: s_tail is stable between the two barriers; < 2 * TGC_BLOCK
-    const bool run_b = avail >= TGC_BLOCK || (last && avail != 0u);
+    const unsigned avail = s_tail - head;  // block-uniform: s_tail is stable between the two barriers; < 2 * BLOCK
+    const bool run_b = avail >= BLOCK || (last && avail != 0u);
     const bool live_b = run_b && threadIdx.x < avail;
     uint32_t e_idx = 0, e_amb = 0;
     if (run_b) {  // block-uniform
-      const unsigned sl = (head + threadIdx.x) & (TGC_RING - 1);
+      const unsigned sl = (head + threadIdx.x) & (RING - 1);
 #pragma unroll
-      for (int k = 0; k < 11; ++k) cfg[k] = live_b ? ring.cfg[k][sl] : 0.f;
+      for (int k = 0; k < 11; ++k) cfg[k] = 0.f;
       if (live_b) {
+        cfg[0] = ring.bx[sl]; cfg[1] = ring.by[sl]; cfg[2] = ring.bth[sl];
         e_idx = ring.idx[sl];
         e_amb = ring.amb0[sl];
+        // survivors keep their input order, so a warp's 32 arm rows are close to each other in memory
+        const float4 a0 = __ldcs(reinterpret_cast<const float4*>(arm) + 2 * (size_t)e_idx);
+        const float4 a1 = __ldcs(reinterpret_cast<const float4*>(arm) + 2 * (size_t)e_idx + 1);
+        cfg[3] = a0.x; cfg[4] = a0.y; cfg[5] = a0.z; cfg[6] = a0.w;
+        cfg[7] = a1.x; cfg[8] = a1.y; cfg[9] = a1.z; cfg[10] = a1.w;
       }
     }
     __syncthreads();
     if (run_b) {
-      tg_stage_b_entry(g, thr, ex, cfg, e_idx, e_amb, valid, qu, ctr, live_b);
-      head += min(avail, (unsigned)TGC_BLOCK);
+      tg_stage_b_entry<COARSE>(g, thr, cg, ex, cfg, e_idx, e_amb, valid, qu, ctr, live_b);
+      head += min(avail, (unsigned)BLOCK);
     }
     if (last) break;
   }
@@ -468,6 +492,7 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
     if (lane == 0) valid[e] = 1;  // provisional; cleared below, by an inline resolve, or by phase 2
     __syncwarp();
     // fixed base: classify the 20 base-pose spheres once, lane k <-> sphere k
+    const TgCoarse cg0 = tg_coarse_init(g, nullptr);  // the edge kernel does not use the coarse grid
     const bool fixed_base = d[0] == 0.f && d[1] == 0.f && d[2] == 0.f;
     uint32_t amb0_shared = 0;
     if (fixed_base && !g.empty) {
@@ -498,8 +523,8 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
       tg_class_clear(cl);
       if (live && !g.empty) {
         const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
-        if (!fixed_base) tg_stage_a(g, thr, p, cl);
-        if (!cl.collide) tg_stage_b<false>(g, thr, p, cfg + 3, cl);  // derived bounds cost the edge kernel 8 %
+        if (!fixed_base) tg_stage_a<false>(g, thr, cg0, p, cl);
+        if (!cl.collide) tg_stage_b<false, false>(g, thr, cg0, p, cfg + 3, cl);  // derived bounds cost the edge kernel 8 %
       }
       if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
       hit = __any_sync(0xffffffffu, live && cl.collide);
@@ -619,8 +644,12 @@ __global__ void k_fill_u8(uint8_t* p, int n, uint8_t v) {
 // resident blocks per SM of the two persistent kernels (queried once per env)
 int tg_query_occupancy(tg_env* env) {
   int a = 0, b = 0;
-  TG_CUDA(cudaFuncSetAttribute(k_check_configs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TgRing)));
-  TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_check_configs, TGC_BLOCK, sizeof(TgRing)));
+  TG_CUDA(cudaFuncSetAttribute(k_check_configs<TGC_BLOCK_PLAIN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)sizeof(TgRing<TGC_BLOCK_PLAIN>)));
+  TG_CUDA(cudaFuncSetAttribute(k_check_configs<TGC_BLOCK_COARSE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)(sizeof(TgRing<TGC_BLOCK_COARSE>) + TG_COARSE_MAX)));
+  TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_check_configs<TGC_BLOCK_PLAIN, false>, TGC_BLOCK_PLAIN,
+                                                        sizeof(TgRing<TGC_BLOCK_PLAIN>)));
   TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_resolve, TGR_BLOCK, 0));
   env->occ_configs = a > 0 ? a : 1;
   env->occ_resolve = b > 0 ? b : 1;
@@ -644,6 +673,14 @@ static inline TgQueue tg_queue_slot(const tg_env* env, int slot) {
 extern "C" int tg_env_set_self_collision(tg_env* env, int on) {
   TG_CHECK_ARG(env != nullptr, "tg_env_set_self_collision: env is NULL");
   env->flags = on ? (env->flags | TG_FLAG_SELF) : (env->flags & ~TG_FLAG_SELF);
+  return TG_OK;
+}
+
+// Test / tuning hook: 0 = never use the coarse far-field variant of the configuration kernel (it is used from
+// TGC_COARSE_MIN_BATCH configurations per launch); the verdicts do not depend on it.
+extern "C" int tg_env_set_coarse(tg_env* env, int on) {
+  TG_CHECK_ARG(env != nullptr, "tg_env_set_coarse: env is NULL");
+  env->no_coarse = on ? 0 : 1;
   return TG_OK;
 }
 
@@ -686,9 +723,15 @@ int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int6
         for (int k = 0; k < 3; ++k) TG_CUDA(cudaEventCreate(&ev[k]));
         TG_CUDA(cudaEventRecord(ev[0], st));
       }
-      const int blocks1 = min(tg_div_up(nb, TGC_BLOCK), env->sm_count * env->occ_configs);
-      k_check_configs<<<blocks1, TGC_BLOCK, sizeof(TgRing), st>>>(env->grid, env->thr, ex, arm + 8 * off, base + 3 * off, nb, valid + off, qu,
-                                                     env->counters_dev);
+      if (nb >= TGC_COARSE_MIN_BATCH && !env->grid.empty && !env->no_coarse) {
+        const size_t smem = sizeof(TgRing<TGC_BLOCK_COARSE>) + (((size_t)env->grid.gnx * env->grid.gny * env->grid.gnz + 15) & ~(size_t)15);
+        k_check_configs<TGC_BLOCK_COARSE, true><<<min(tg_div_up(nb, TGC_BLOCK_COARSE), env->sm_count), TGC_BLOCK_COARSE, smem, st>>>(
+            env->grid, env->thr, ex, arm + 8 * off, base + 3 * off, nb, valid + off, qu, env->counters_dev);
+      } else {
+        const int blocks1 = min(tg_div_up(nb, TGC_BLOCK_PLAIN), env->sm_count * env->occ_configs);
+        k_check_configs<TGC_BLOCK_PLAIN, false><<<blocks1, TGC_BLOCK_PLAIN, sizeof(TgRing<TGC_BLOCK_PLAIN>), st>>>(
+            env->grid, env->thr, ex, arm + 8 * off, base + 3 * off, nb, valid + off, qu, env->counters_dev);
+      }
       if (env->timing) TG_CUDA(cudaEventRecord(ev[1], st));
       if (!env->grid.empty) {
         k_resolve<<<env->sm_count * env->occ_resolve, TGR_BLOCK, 0, st>>>(env->grid, qu, valid + off, env->counters_dev);

@@ -67,6 +67,45 @@ __device__ __forceinline__ int tg_probe_if(const TgGrid& g, bool need, float gx,
 #endif
 }
 
+// Coarse far-field grid in SHARED memory (phase 1 of the configuration kernel).  One byte per block of cg_r^3 voxels =
+// a lower bound on the distance from any point of the block to the cloud (K1, k_edt_z_coarse).  A sphere whose centre
+// reads a code >= thr.cfree_ge[k] is proven free without touching the L2-resident fine grid: the look-up is ~12 ALU
+// instructions and one LDS, while a fine probe costs one L1-miss request - the resource that bounds this kernel.
+struct TgCoarse {
+  const uint8_t* s;  // shared-memory copy, [gnz][gny][gnx]
+  int nx1, ny1, nz1; // gn - 1
+  int nx, nxy;
+  float inv_r, b0, b1, b2;  // block index = floor((g + tex_bias) * inv_r)
+};
+#define TG_FLOOR_MAGIC 12582912.0f      // 1.5 * 2^23: x + this, rounded DOWN, holds floor(x) in its mantissa for |x| < 2^22
+#define TG_FLOOR_MAGIC_BITS 0x4B400000
+__device__ __forceinline__ TgCoarse tg_coarse_init(const TgGrid& g, const uint8_t* smem) {
+  TgCoarse c;
+  c.s = smem;
+  c.nx1 = g.gnx - 1; c.ny1 = g.gny - 1; c.nz1 = g.gnz - 1;
+  c.nx = g.gnx; c.nxy = g.gnx * g.gny;
+  c.inv_r = g.cg_inv_r;
+  c.b0 = g.tex_bias[0] * g.cg_inv_r + TG_FLOOR_MAGIC; c.b1 = g.tex_bias[1] * g.cg_inv_r + TG_FLOOR_MAGIC;
+  c.b2 = g.tex_bias[2] * g.cg_inv_r + TG_FLOOR_MAGIC;
+  return c;
+}
+__device__ __forceinline__ int tg_coarse_code(const TgCoarse& c, float gx, float gy, float gz) {
+  // Block index per axis = floor(g * inv_r + b): ONE round-down FMA with the 1.5 * 2^23 bias folded into b leaves the
+  // integer in the mantissa (no F2I: the conversion unit runs at quarter rate and this kernel is issue-bound), and ONE
+  // DPX add-min-relu subtracts the bias pattern and clamps to [0, n - 1].  Points outside the grid read the nearest
+  // boundary block, whose bound holds for them too (projecting onto the box does not increase the distance to a point
+  // inside it).  |g * inv_r| stays far below 2^22.
+  const int ix = __viaddmin_s32_relu(__float_as_int(__fmaf_rd(gx, c.inv_r, c.b0)), -TG_FLOOR_MAGIC_BITS, c.nx1);
+  const int iy = __viaddmin_s32_relu(__float_as_int(__fmaf_rd(gy, c.inv_r, c.b1)), -TG_FLOOR_MAGIC_BITS, c.ny1);
+  const int iz = __viaddmin_s32_relu(__float_as_int(__fmaf_rd(gz, c.inv_r, c.b2)), -TG_FLOOR_MAGIC_BITS, c.nz1);
+  TG_STAT_LANE(13, 1);
+  return (int)c.s[iz * c.nxy + iy * c.nx + ix];
+}
+
+#ifndef TG_COARSE_MEMBERS
+#define TG_COARSE_MEMBERS 0  // 1: members of a cull group whose enclosing sphere was not proven free also try the coarse grid
+#endif
+
 struct TgClass {
   bool collide;
   uint32_t amb[4];
@@ -105,34 +144,43 @@ __device__ __forceinline__ TgPose tg_pose(const TgGrid& g, float bx, float by, f
 // source free - a per-sphere version of the all-or-nothing group test.  A skipped sphere reads TG_CODE_SKIPPED: free,
 // never ambiguous.  The edge kernel does not use it (measured 8 % slower there: more predicates, same loads).
 #define TG_CODE_SKIPPED (1 << 20)
-template <int K, bool DERIVE>
-__device__ __forceinline__ int tg_probe_k(const TgGrid& g, const TgThr& thr, int bcode, float gx, float gy, float gz) {
+template <int K, bool DERIVE, bool C>
+__device__ __forceinline__ int tg_probe_k(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, int bcode, float gx, float gy, float gz) {
+  bool need = true;
 #ifndef TG_NO_DERIVED_BOUNDS
-  if constexpr (DERIVE && tgm_k_src(K) >= 0) return tg_probe_if(g, bcode < thr.src_ge[K], gx, gy, gz, TG_CODE_SKIPPED);
+  if constexpr (DERIVE && tgm_k_src(K) >= 0) need = bcode < thr.src_ge[K];
 #endif
-  return tg_probe(g, gx, gy, gz);
+  if constexpr (C) {
+    need = need && tg_coarse_code(cg, gx, gy, gz) < thr.cfree_ge[K];
+    return tg_probe_if(g, need, gx, gy, gz, TG_CODE_SKIPPED);
+  } else {
+#ifndef TG_NO_DERIVED_BOUNDS
+    if constexpr (DERIVE && tgm_k_src(K) >= 0) return tg_probe_if(g, need, gx, gy, gz, TG_CODE_SKIPPED);
+#endif
+    return tg_probe(g, gx, gy, gz);
+  }
 }
 
 // spheres [K0, K1) of a frame whose rotation is the base yaw only:  p_base = l + (tx, 0, tz).
 // All loads of the group are issued before the first classification (memory-level parallelism).
 // DERIVE: bcode is the code read at the centre of the group's enclosing sphere.
-template <int K, int K1, int K0, bool DERIVE>
-__device__ __forceinline__ void tg_probe_yaw(const TgGrid& g, const TgThr& thr, const TgPose& p, float gtx, float gty, float gtz,
-                                             int bcode, int (&code)[K1 - K0]) {
+template <int K, int K1, int K0, bool DERIVE, bool C>
+__device__ __forceinline__ void tg_probe_yaw(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, float gtx, float gty,
+                                             float gtz, int bcode, int (&code)[K1 - K0]) {
   if constexpr (K < K1) {
     const float4 l = TGM_K_SPH[K];
     const float gx = fmaf(p.cs, l.x, fmaf(-p.sn, l.y, gtx));
     const float gy = fmaf(p.sn, l.x, fmaf(p.cs, l.y, gty));
     const float gz = fmaf(g.vpm, l.z, gtz);
-    code[K - K0] = tg_probe_k<K, DERIVE>(g, thr, bcode, gx, gy, gz);
-    tg_probe_yaw<K + 1, K1, K0, DERIVE>(g, thr, p, gtx, gty, gtz, bcode, code);
+    code[K - K0] = tg_probe_k<K, DERIVE, C>(g, thr, cg, bcode, gx, gy, gz);
+    tg_probe_yaw<K + 1, K1, K0, DERIVE, C>(g, thr, cg, p, gtx, gty, gtz, bcode, code);
   }
 }
-template <int K0, int K1, bool DERIVE = false>
-__device__ __forceinline__ void tg_group_yaw(const TgGrid& g, const TgThr& thr, const TgPose& p, float gtx, float gty, float gtz,
-                                             TgClass& out, int bcode = 0) {
+template <int K0, int K1, bool DERIVE, bool C>
+__device__ __forceinline__ void tg_group_yaw(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, float gtx, float gty,
+                                             float gtz, TgClass& out, int bcode = 0) {
   int code[K1 - K0];
-  tg_probe_yaw<K0, K1, K0, DERIVE>(g, thr, p, gtx, gty, gtz, bcode, code);
+  tg_probe_yaw<K0, K1, K0, DERIVE, C>(g, thr, cg, p, gtx, gty, gtz, bcode, code);
 #pragma unroll
   for (int k = K0; k < K1; ++k) TG_CLASSIFY_ONE(k, code[k - K0]);
 }
@@ -153,56 +201,62 @@ __device__ __forceinline__ void tg_vox_frame(const TgGrid& g, const TgPose& p, c
   V.gt[2] = g.vpm * F.t[2];
 }
 
-template <int K, int K1, int K0, bool DERIVE>
-__device__ __forceinline__ void tg_probe_arm(const TgGrid& g, const TgThr& thr, const TgVox& V, int bcode, int (&code)[K1 - K0]) {
+template <int K, int K1, int K0, bool DERIVE, bool C>
+__device__ __forceinline__ void tg_probe_arm(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgVox& V, int bcode,
+                                             int (&code)[K1 - K0]) {
   if constexpr (K < K1) {
     const float4 l = TGM_K_SPH[K];
     const float gx = fmaf(V.G[0], l.x, fmaf(V.G[1], l.y, fmaf(V.G[2], l.z, V.gt[0])));
     const float gy = fmaf(V.G[3], l.x, fmaf(V.G[4], l.y, fmaf(V.G[5], l.z, V.gt[1])));
     const float gz = fmaf(V.G[6], l.x, fmaf(V.G[7], l.y, fmaf(V.G[8], l.z, V.gt[2])));
-    code[K - K0] = tg_probe_k<K, DERIVE>(g, thr, bcode, gx, gy, gz);
-    tg_probe_arm<K + 1, K1, K0, DERIVE>(g, thr, V, bcode, code);
+    code[K - K0] = tg_probe_k<K, DERIVE, C>(g, thr, cg, bcode, gx, gy, gz);
+    tg_probe_arm<K + 1, K1, K0, DERIVE, C>(g, thr, cg, V, bcode, code);
   }
 }
-template <int K0, int K1, bool DERIVE>
-__device__ __forceinline__ void tg_group_arm(const TgGrid& g, const TgThr& thr, const TgVox& V, int bcode, TgClass& out) {
+template <int K0, int K1, bool DERIVE, bool C>
+__device__ __forceinline__ void tg_group_arm(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgVox& V, int bcode, TgClass& out) {
   int code[K1 - K0];
-  tg_probe_arm<K0, K1, K0, DERIVE>(g, thr, V, bcode, code);
+  tg_probe_arm<K0, K1, K0, DERIVE, C>(g, thr, cg, V, bcode, code);
 #pragma unroll
   for (int k = K0; k < K1; ++k) TG_CLASSIFY_ONE(k, code[k - K0]);
 }
 
 // enclosing-sphere probes (cull groups, fetch_model.cuh TGM_BOUND): true = the whole group is free
-template <int B>
-__device__ __forceinline__ int tg_bound_code_yaw(const TgGrid& g, const TgPose& p, float gtx, float gty, float gtz) {
+template <int B, bool C>
+__device__ __forceinline__ int tg_bound_code_yaw(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, float gtx, float gty,
+                                                 float gtz) {
   const float4 l = TGM_BOUND[B];
-  return tg_probe(g, fmaf(p.cs, l.x, fmaf(-p.sn, l.y, gtx)), fmaf(p.sn, l.x, fmaf(p.cs, l.y, gty)), fmaf(g.vpm, l.z, gtz));
+  const float gx = fmaf(p.cs, l.x, fmaf(-p.sn, l.y, gtx)), gy = fmaf(p.sn, l.x, fmaf(p.cs, l.y, gty)), gz = fmaf(g.vpm, l.z, gtz);
+  if constexpr (C) return tg_probe_if(g, tg_coarse_code(cg, gx, gy, gz) < thr.cbound_ge[B], gx, gy, gz, TG_CODE_SKIPPED);
+  return tg_probe(g, gx, gy, gz);
 }
 // Stage A: the 20 spheres that only depend on the base pose (base_link + torso_fixed), largest first.
 // Most colliding configurations are refuted by the first group of three.
-__device__ __forceinline__ void tg_stage_a(const TgGrid& g, const TgThr& thr, const TgPose& p, TgClass& out) {
+template <bool C>
+__device__ __forceinline__ void tg_stage_a(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, TgClass& out) {
   // the largest base sphere alone refutes 55 % of the bench's configurations, the three big ones 65 %
 #ifndef TG_STAGE_A_NOSPLIT
-  tg_group_yaw<0, 1>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  tg_group_yaw<0, 1, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
   if (out.collide) return;
-  tg_group_yaw<1, 3>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  tg_group_yaw<1, 3, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
 #else
-  tg_group_yaw<0, 3>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  tg_group_yaw<0, 3, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
 #endif
   if (out.collide) return;
   // (enclosing-sphere probes for the torso column and the bumper arc were measured: they rarely prove anything inside
   // a 0.32 m window and cost 1 % more than they save)
-  tg_group_yaw<3, 9>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  tg_group_yaw<3, 9, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
   if (out.collide) return;
-  tg_group_yaw<9, 20>(g, thr, p, p.gx0, p.gy0, 0.f, out);
+  tg_group_yaw<9, 20, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
 }
 
-template <int B>
-__device__ __forceinline__ int tg_bound_code_arm(const TgGrid& g, const TgVox& V) {
+template <int B, bool C>
+__device__ __forceinline__ int tg_bound_code_arm(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgVox& V) {
   const float4 l = TGM_BOUND[B];
   const float gx = fmaf(V.G[0], l.x, fmaf(V.G[1], l.y, fmaf(V.G[2], l.z, V.gt[0])));
   const float gy = fmaf(V.G[3], l.x, fmaf(V.G[4], l.y, fmaf(V.G[5], l.z, V.gt[1])));
   const float gz = fmaf(V.G[6], l.x, fmaf(V.G[7], l.y, fmaf(V.G[8], l.z, V.gt[2])));
+  if constexpr (C) return tg_probe_if(g, tg_coarse_code(cg, gx, gy, gz) < thr.cbound_ge[B], gx, gy, gz, TG_CODE_SKIPPED);
   return tg_probe(g, gx, gy, gz);
 }
 
@@ -210,26 +264,26 @@ __device__ __forceinline__ int tg_bound_code_arm(const TgGrid& g, const TgVox& V
 // The small spheres are grouped (head, ears, one group per arm link); one probe at the centre of a
 // group's enclosing sphere that proves it free skips the whole group, which is the common case for a
 // free configuration away from the surfaces.
-template <bool DERIVE>
-__device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, const TgPose& p, const float* q, TgClass& out) {
+template <bool DERIVE, bool C>
+__device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, const float* q, TgClass& out) {
   const float tz = TGM_OFF_TORSO_Z + q[0];
   {
     const float gtx1 = fmaf(p.cs, TGM_OFF_TORSO_X, p.gx0), gty1 = fmaf(p.sn, TGM_OFF_TORSO_X, p.gy0), gtz1 = g.vpm * tz;
-    const int b0 = tg_bound_code_yaw<0>(g, p, gtx1, gty1, gtz1);
-    const int b1 = tg_bound_code_yaw<1>(g, p, gtx1, gty1, gtz1);
-    const int b2 = tg_bound_code_yaw<2>(g, p, gtx1, gty1, gtz1);
-    tg_group_yaw<20, 28>(g, thr, p, gtx1, gty1, gtz1, out);
+    const int b0 = tg_bound_code_yaw<0, C>(g, thr, cg, p, gtx1, gty1, gtz1);
+    const int b1 = tg_bound_code_yaw<1, C>(g, thr, cg, p, gtx1, gty1, gtz1);
+    const int b2 = tg_bound_code_yaw<2, C>(g, thr, cg, p, gtx1, gty1, gtz1);
+    tg_group_yaw<20, 28, false, C>(g, thr, cg, p, gtx1, gty1, gtz1, out);
     if (out.collide) return;
     if (b0 < thr.bound_ge[0]) {
-      tg_group_yaw<28, 33, DERIVE>(g, thr, p, gtx1, gty1, gtz1, out, b0);
+      tg_group_yaw<28, 33, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, p, gtx1, gty1, gtz1, out, b0);
       if (out.collide) return;
     }
     if (b1 < thr.bound_ge[1]) {
-      tg_group_yaw<33, 44, DERIVE>(g, thr, p, gtx1, gty1, gtz1, out, b1);
+      tg_group_yaw<33, 44, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, p, gtx1, gty1, gtz1, out, b1);
       if (out.collide) return;
     }
     if (b2 < thr.bound_ge[2]) {
-      tg_group_yaw<44, 55, DERIVE>(g, thr, p, gtx1, gty1, gtz1, out, b2);
+      tg_group_yaw<44, 55, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, p, gtx1, gty1, gtz1, out, b2);
       if (out.collide) return;
     }
   }
@@ -240,46 +294,46 @@ __device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, co
   T.t[2] = tz;
   tg_frame_child(T, TGM_OFF_SHOULDER_PAN_X, TGM_OFF_SHOULDER_PAN_Y, TGM_OFF_SHOULDER_PAN_Z, 4, q[1], F);
   tg_vox_frame(g, p, F, V);
-  if (const int bc = tg_bound_code_arm<3>(g, V); bc < thr.bound_ge[3]) {
-    tg_group_arm<55, 59, DERIVE>(g, thr, V, bc, out);
+  if (const int bc = tg_bound_code_arm<3, C>(g, thr, cg, V); bc < thr.bound_ge[3]) {
+    tg_group_arm<55, 59, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(F, TGM_OFF_SHOULDER_LIFT_X, TGM_OFF_SHOULDER_LIFT_Y, TGM_OFF_SHOULDER_LIFT_Z, 3, q[2], H);
   tg_vox_frame(g, p, H, V);
-  if (const int bc = tg_bound_code_arm<4>(g, V); bc < thr.bound_ge[4]) {
-    tg_group_arm<59, 66, DERIVE>(g, thr, V, bc, out);
+  if (const int bc = tg_bound_code_arm<4, C>(g, thr, cg, V); bc < thr.bound_ge[4]) {
+    tg_group_arm<59, 66, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(H, TGM_OFF_UPPERARM_ROLL_X, TGM_OFF_UPPERARM_ROLL_Y, TGM_OFF_UPPERARM_ROLL_Z, 2, q[3], F);
   tg_vox_frame(g, p, F, V);
-  if (const int bc = tg_bound_code_arm<5>(g, V); bc < thr.bound_ge[5]) {
-    tg_group_arm<66, 74, DERIVE>(g, thr, V, bc, out);
+  if (const int bc = tg_bound_code_arm<5, C>(g, thr, cg, V); bc < thr.bound_ge[5]) {
+    tg_group_arm<66, 74, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(F, TGM_OFF_ELBOW_FLEX_X, TGM_OFF_ELBOW_FLEX_Y, TGM_OFF_ELBOW_FLEX_Z, 3, q[4], H);
   tg_vox_frame(g, p, H, V);
-  if (const int bc = tg_bound_code_arm<6>(g, V); bc < thr.bound_ge[6]) {
-    tg_group_arm<74, 80, DERIVE>(g, thr, V, bc, out);
+  if (const int bc = tg_bound_code_arm<6, C>(g, thr, cg, V); bc < thr.bound_ge[6]) {
+    tg_group_arm<74, 80, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(H, TGM_OFF_FOREARM_ROLL_X, TGM_OFF_FOREARM_ROLL_Y, TGM_OFF_FOREARM_ROLL_Z, 2, q[5], F);
   tg_vox_frame(g, p, F, V);
-  if (const int bc = tg_bound_code_arm<7>(g, V); bc < thr.bound_ge[7]) {
-    tg_group_arm<80, 87, DERIVE>(g, thr, V, bc, out);
+  if (const int bc = tg_bound_code_arm<7, C>(g, thr, cg, V); bc < thr.bound_ge[7]) {
+    tg_group_arm<80, 87, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(F, TGM_OFF_WRIST_FLEX_X, TGM_OFF_WRIST_FLEX_Y, TGM_OFF_WRIST_FLEX_Z, 3, q[6], H);
   tg_vox_frame(g, p, H, V);
-  if (const int bc = tg_bound_code_arm<8>(g, V); bc < thr.bound_ge[8]) {
-    tg_group_arm<87, 93, DERIVE>(g, thr, V, bc, out);
+  if (const int bc = tg_bound_code_arm<8, C>(g, thr, cg, V); bc < thr.bound_ge[8]) {
+    tg_group_arm<87, 93, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc, out);
     if (out.collide) return;
   }
   tg_frame_child(H, TGM_OFF_WRIST_ROLL_X, TGM_OFF_WRIST_ROLL_Y, TGM_OFF_WRIST_ROLL_Z, 2, q[7], F);
   tg_vox_frame(g, p, F, V);
-  if (const int bc = tg_bound_code_arm<9>(g, V); bc < thr.bound_ge[9]) {
-    tg_group_arm<93, 99, DERIVE>(g, thr, V, bc, out);
+  if (const int bc = tg_bound_code_arm<9, C>(g, thr, cg, V); bc < thr.bound_ge[9]) {
+    tg_group_arm<93, 99, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc, out);
     if (out.collide) return;
-    tg_group_arm<99, 111, DERIVE>(g, thr, V, bc, out);
+    tg_group_arm<99, 111, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc, out);
   }
 }
 

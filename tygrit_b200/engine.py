@@ -131,6 +131,14 @@ class CollisionWorld:
         k = ("n_points", "n_dropped", "nx", "ny", "nz", "cells", "voxels_per_metre", "slack")
         return dict(zip(k, [float(v) for v in out]))
 
+    def grid_info(self) -> dict[str, float]:
+        """Layout of the built structure inside the blob (tests / tools)."""
+        out = (C.c_double * 20)()
+        N.check(self._lib.tg_env_grid_info(self._h, out), "tg_env_grid_info")
+        k = ("empty", "nx", "ny", "nz", "bias_x", "bias_y", "bias_z", "voxels_per_metre", "q", "slack", "window", "off_df", "off_cg",
+             "gnx", "gny", "gnz", "cg_r", "cg_q")
+        return dict(zip(k, [float(v) for v in out]))
+
     def counters(self) -> dict[str, int]:
         """Counters since the last call (synchronises the current stream)."""
         out = (C.c_int64 * 4)()
@@ -141,6 +149,10 @@ class CollisionWorld:
     def set_queue_limit(self, items: int) -> None:
         """Test hook: shrink the ambiguous queue (0 = whole queue) to exercise the inline overflow path."""
         N.check(self._lib.tg_env_set_queue_limit(self._h, int(items)), "tg_env_set_queue_limit")
+
+    def set_coarse(self, on: bool) -> None:
+        """Test / tuning hook: switch the shared-memory coarse far-field variant of the configuration kernel on or off."""
+        N.check(self._lib.tg_env_set_coarse(self._h, int(bool(on))), "tg_env_set_coarse")
 
     def set_timing(self, on: bool) -> None:
         N.check(self._lib.tg_env_set_timing(self._h, int(bool(on))), "tg_env_set_timing")

@@ -237,6 +237,49 @@ int tg_check_occlusion(const double* q10, const double* target, int64_t n_target
  * subgoal_generator/samplers/grasp_sampler.py:109-137 after one tg_check_configs call.  */
 int tg_first_valid(const uint8_t* valid, int64_t B, int group, int32_t* first, void* stream);
 
+/* ---- device-resident planners (replace the VAMP planners TyGrit calls in
+ *      planning/fetch/algorithms.py:23-232).  Configuration vectors are 11 floats [x, y, theta, q0..q7]; theta is an
+ *      angle (shortest arc).  Trees, lattice, roadmap, candidate edges and verdicts stay in device memory; the host
+ *      enqueues kernels and polls a status word in mapped pinned memory; a finished path is the only device->host copy. */
+typedef struct tg_planner tg_planner;
+int tg_planner_create(tg_planner** out, tg_env* env, int max_nodes, int batch);
+int tg_planner_destroy(tg_planner* p);
+/* plan_arm_rrtc / planner_func(start, goal, env, settings, sampler) (algorithms.py:23-37): batched RRT-Connect with a
+ * Halton sampler (vamp_preview.py:58-59).  start, goal, lo, hi: HOST 11 floats; a dimension with lo == hi is not sampled
+ * (arm-only planning fixes the base).  path_out: HOST max_path x 11.  *n_path = 0: no path within max_iters / timeout. */
+int tg_planner_rrt_connect(tg_planner* p, const float* start, const float* goal, const float* lo, const float* hi, float range,
+                           int max_iters, uint32_t halton_skip, int rake, float resolution, double timeout_s, float* path_out,
+                           int max_path, int* n_path, int* iterations, void* stream);
+/* module.simplify / whole_body_simplify (algorithms.py:51,124): all waypoint pairs validated in one batch, then the
+ * shortest path through the valid skips.  path: HOST n x 11 in/out (n <= 128).                                     */
+int tg_planner_shortcut(tg_planner* p, float* path, int* n_io, int rake, float resolution, void* stream);
+/* Base layer of multilayer_rrtc (algorithms.py:77-147, HybridAStarConfig.reverse_penalty = 50): SE(2) lattice search
+ * (grid `res` metres x 16 headings; forward / backward x reverse_penalty / turn in place), cost-to-go by parallel
+ * relaxation, lazy whole-body edge validation with the arm held at arm8.  start, goal: HOST [x, y, theta]; bounds4 HOST
+ * {x0, x1, y0, y1}; path_out HOST max_path x 3; stats3 HOST {sweeps, validation rounds, lattice nodes} or NULL.      */
+int tg_planner_base_path(tg_planner* p, const float* start, const float* goal, const float* arm8, const float* bounds4, float res,
+                         float reverse_penalty, float turn_cost, int rake, float resolution, int max_rounds, float* path_out,
+                         int max_path, int* n_path, double* stats3, void* stream);
+/* fcit_wb (algorithms.py:155-232: FCITSettings batch_size / max_samples / max_iterations / reverse_weight, XY bounds):
+ * lazily evaluated fully connected roadmap over Halton samples.  stats4 HOST {samples drawn, roadmap nodes, lazy rounds,
+ * relaxation sweeps} or NULL.                                                                                        */
+int tg_planner_fcit(tg_planner* p, const float* start, const float* goal, const float* lo, const float* hi, int batch_size,
+                    int max_samples, int max_rounds, float reverse_weight, float max_edge, uint32_t halton_skip, int rake,
+                    float resolution, double timeout_s, float* path_out, int max_path, int* n_path, double* stats4, void* stream);
+
+/* ---- receding-horizon step as one CUDA graph (BASELINE config 5) ------------------- */
+/* One scheduler step of the reference = update_environment (full rebuild, vamp_preview.py:183-240) + planning, i.e.
+ * edge validation (planning/fetch/algorithms.py:37,51).  tg_c5_run captures [device-generated fresh edges ->
+ * tg_env_build(clouds[i]) -> tg_check_edges] once per cloud buffer as a CUDA graph (fixed bounds required:
+ * tg_env_set_bounds) and replays graph[i % n_clouds] for `steps` steps, timing with CUDA events from C - no host loop
+ * in Python, no per-kernel launch overhead.  clouds: HOST array of n_clouds DEVICE pointers (n x 3 f32) with their point
+ * counts; E arm-only edges per step at random bases inside base_box4 = {x0, x1, y0, y1} (HOST).  out8 (HOST doubles):
+ * ms per step, ms per build-only replay, valid-edge fraction, configuration checks per step, graphs captured, nodes
+ * per step graph, min / max step ms (sampled every 10th step).  Synchronous.  The blob header of the env is not
+ * meaningful afterwards (rebuild before exporting).                                                              */
+int tg_c5_run(tg_env* env, const float* const* clouds, const int64_t* n_points, int n_clouds, int64_t E, int steps,
+              int warmup, uint64_t seed, const float* base_box4, int rake, float resolution, double* out8);
+
 /* ---- synthetic input (benchmark support, not part of the reference surface) ----- */
 /* Analytic head-camera depth frames: rays against the 8 x 6 x 2.6 m room shell, `nb`
  * furniture boxes (DEVICE nb x 6: lo xyz, hi xyz; nb <= 64) and the robot's own 111

@@ -667,3 +667,26 @@ def test_streaming_self_filter_full_resolution_vs_oracle():
         assert not mask[s][~keep].any()
         removed += int((signed < 0).sum())
     assert removed > 1000
+
+
+def test_replanning_step_graph_runner():
+    """BASELINE config 5 as CUDA-graph replays timed from C (tg_c5_run): fixed bounds required, the world left behind is
+    the last cloud's (verdicts vs the oracle), every step validates fresh edges, and a build after it still works."""
+    clouds_np = [synth.room_cloud(60_000 + 20_000 * i, perturb_step=i) for i in range(3)]
+    w = CollisionWorld(max_points=1 << 18)
+    with pytest.raises(RuntimeError):
+        w.run_replanning_steps([_cuda(c) for c in clouds_np], 1000, steps=2)       # no fixed bounds
+    w.set_bounds((-4.2, -3.2, 0.2), (4.2, 3.2, 2.8))
+    r = w.run_replanning_steps([_cuda(c) for c in clouds_np], 20_000, steps=9, warmup=2, seed=3)
+    assert r["graphs"] == 6 and r["nodes_per_step_graph"] >= 10
+    assert 0.0 < r["build_ms"] < r["ms_per_step"] < 50.0
+    assert 0.02 < r["valid_fraction"] < 0.5 and r["config_checks_per_step"] > 20_000 * 8 * 10
+    # 9 steps over 3 clouds: the last replay built clouds[2]
+    arm, base = synth.random_configs(20_000, seed=12)
+    got = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    _assert_verdicts(got, cchecker.CCloud(clouds_np[2]).clearance(arm, base, cap=1e-3), "after graph replays")
+    r2 = w.run_replanning_steps([_cuda(c) for c in clouds_np], 20_000, steps=9, warmup=2, seed=4)
+    assert abs(r2["valid_fraction"] - r["valid_fraction"]) < 0.05 and r2["valid_fraction"] != r["valid_fraction"]   # other edges
+    w.build(_cuda(clouds_np[0]))
+    got = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
+    _assert_verdicts(got, cchecker.CCloud(clouds_np[0]).clearance(arm, base, cap=1e-3), "rebuild after graph replays")

@@ -35,7 +35,7 @@ def test_plan_arm_empty_env(planner):
     for cfg in res.trajectory.arm_path:
         assert cfg.shape == (8,)
     assert res.trajectory.base_configs[0] == SE2Pose(0.0, 0.0, 0.0)
-    assert "planning_time_ms" in res.stats
+    assert "planning_time_ms" in res.stats and "planning_iterations" in res.stats   # the reference's keys (algorithms.py:43-44)
 
 
 def test_add_clear_pointcloud_and_spheres(planner):
@@ -47,6 +47,53 @@ def test_add_clear_pointcloud_and_spheres(planner):
     assert not planner.validate_config(wb)
     planner.clear_spheres()
     assert planner.validate_config(wb)
+
+
+def test_pointclouds_accumulate_until_cleared(planner):
+    """vamp_preview.Environment.add_pointcloud ADDS geometry until clear_pointclouds (vamp_preview.py:205-240)."""
+    planner.clear_pointclouds()
+    wb = WholeBodyConfig(np.array(_READY), SE2Pose(0.0, 0.0, 0.0))
+    near_arm = np.array([[0.9, 0.0, 0.78]], dtype=np.float64)          # on the stretched arm
+    far = np.array([[3.0, 3.0, 1.0], [3.1, 3.0, 1.0]], dtype=np.float64)
+    planner.add_pointcloud(near_arm)
+    assert not planner.validate_config(wb)
+    planner.add_pointcloud(far)                                        # a second cloud must not drop the first
+    assert not planner.validate_config(wb)
+    planner.clear_pointclouds()
+    planner.add_pointcloud(far)
+    assert planner.validate_config(wb)
+    planner.clear_pointclouds()
+
+
+def test_sphere_capacity_checked_before_mutating(planner):
+    planner.clear_spheres()
+    for i in range(64):
+        planner.add_sphere([5.0 + i, 5.0, 1.0], 0.05)
+    with pytest.raises(RuntimeError):
+        planner.add_sphere([0.9, 0.0, 0.75], 0.1)                      # the 65th: rejected, host list and device in step
+    assert len(planner._obstacles) == 64
+    assert planner.validate_config(WholeBodyConfig(np.array(_READY), SE2Pose(0.0, 0.0, 0.0)))
+    planner.clear_spheres()
+
+
+def test_unknown_algorithm_names_raise():
+    for kw in ({"algorithm": "prm"}, {"whole_body_algorithm": "nope"}, {"sampler": "xorshift"}):
+        with pytest.raises(ValueError):
+            create_planner("fetch", "b200", config=B200PlannerConfig(max_points=1 << 12, **kw))
+
+
+def test_self_collision_is_part_of_the_planner_verdict(planner):
+    """B200Planner enables the self-collision term (VAMP's validate_whole_body_config tests the robot against itself)."""
+    from oracle import cchecker
+
+    planner.clear_pointclouds()
+    arm, base = synth.random_configs(4000, seed=77)
+    cl = cchecker.self_clearance(arm)
+    ok = np.asarray(planner.validate_configs(arm, base))
+    d = np.abs(cl) > 1e-5
+    assert np.array_equal(ok[d], (cl > 0)[d]) and 0.05 < (~ok).mean() < 0.3
+    i = int(np.flatnonzero(cl < -1e-3)[0])
+    assert planner.validate_config(WholeBodyConfig(arm[i].astype(np.float64), SE2Pose(0.0, 0.0, 0.0))) is False
 
 
 def test_attach_detach(planner):
@@ -61,7 +108,9 @@ def test_update_environment_and_verdicts_match_oracle(planner):
     cloud = synth.tabletop_cloud(50_000)
     planner.update_environment(cloud, SE2Pose(0.0, 0.0, 0.0))
     arm, base = synth.random_configs(64, seed=5, base_box=(-1, 1, -1, 1))
-    cl = collide.CloudOracle(cloud).config_clearance(arm, base)
+    from oracle import cchecker
+
+    cl = np.minimum(collide.CloudOracle(cloud).config_clearance(arm, base), cchecker.self_clearance(arm))   # the planner's verdict
     for i in range(64):
         if abs(cl[i]) > 1e-5:
             wb = WholeBodyConfig(arm[i].astype(np.float64), SE2Pose(*map(float, base[i])))
@@ -94,6 +143,72 @@ def test_plan_whole_body_and_failures(planner):
     res = planner.plan_whole_body(goal, start)
     assert not res.success and res.failure == PlannerFailure.COLLISION_AT_START
     planner.clear_pointclouds()
+
+
+def _room_planner(algo):
+    p = create_planner("fetch", "b200", config=B200PlannerConfig(max_points=1 << 19, whole_body_algorithm=algo, timeout=20.0))
+    cloud = synth.room_cloud(150_000)
+    p.update_environment(cloud, SE2Pose(0.0, 0.0, 0.0))
+    return p, cloud
+
+
+def _free_base_poses(p, n, seed):
+    import torch
+
+    arm, base, _ = synth.free_base_configs(p.world, n, seed=seed, device=torch.device("cuda", 0), base_box=(-3.2, 3.2, -2.2, 2.2))
+    return base.cpu().numpy().astype(np.float64)
+
+
+@pytest.mark.parametrize("algo", ["multilayer_rrtc", "fcit_wb", "rrtc_wb"])
+def test_whole_body_algorithms_in_the_room(algo):
+    """Every whole_body_algorithm plans between free poses of the furnished room; the returned trajectory is collision-free
+    per the ORACLE (cloud + self-collision) at every waypoint, starts / ends at the request and turns along the short arc."""
+    from oracle import cchecker
+
+    p, cloud = _room_planner(algo)
+    poses = _free_base_poses(p, 8, seed=3)
+    cc = cchecker.CCloud(cloud)
+    solved = 0
+    for i in range(0, 6, 2):
+        s = WholeBodyConfig(np.array(_TUCK), SE2Pose(*poses[i]))
+        g = WholeBodyConfig(np.array(_TUCK if i % 4 else [0.2, 1.0, 0.8, 0.0, 1.2, 0.0, 1.0, 0.0]), SE2Pose(*poses[i + 1]))
+        if not (p.validate_config(s) and p.validate_config(g)):
+            continue
+        res = p.plan_whole_body(s, g)
+        if not res.success:
+            assert res.failure == PlannerFailure.NO_PATH_FOUND
+            continue
+        solved += 1
+        arm = np.asarray(res.trajectory.arm_path)
+        base = np.array([[b.x, b.y, b.theta] for b in res.trajectory.base_configs])
+        np.testing.assert_allclose(arm[0], s.arm_joints, atol=1e-6)
+        np.testing.assert_allclose(arm[-1], g.arm_joints, atol=1e-6)
+        np.testing.assert_allclose(base[0], poses[i], atol=1e-6)
+        np.testing.assert_allclose(base[-1, :2], poses[i + 1, :2], atol=1e-6)
+        assert abs(np.angle(np.exp(1j * (base[-1, 2] - poses[i + 1, 2])))) < 1e-5         # same heading modulo 2 pi
+        assert np.abs(np.diff(base[:, 2])).max() < 0.5                                   # no 2 pi jumps between waypoints
+        cl = np.minimum(cc.clearance(arm.astype(np.float32), base.astype(np.float32), cap=1e-3), cchecker.self_clearance(arm.astype(np.float32)))
+        assert (cl > -1e-5).all(), f"{algo}: waypoint in collision per the oracle (min clearance {cl.min()})"
+        assert p.check_trajectory_collisions(arm.tolist(), base.tolist()) is False
+        assert "total_planning_time_ms" in res.stats
+    assert solved >= 2, f"{algo}: only {solved} of 3 queries solved"
+
+
+def test_multilayer_base_layer_prefers_driving_forward():
+    """reverse_penalty = 50 (algorithms.py:93-96): to reach a pose 1.5 m BEHIND it in free space the robot turns round
+    rather than reversing all the way."""
+    p = create_planner("fetch", "b200", config=B200PlannerConfig(max_points=1 << 12))
+    p.clear_pointclouds()
+    s = WholeBodyConfig(np.array(_TUCK), SE2Pose(0.0, 0.0, 0.0))
+    g = WholeBodyConfig(np.array(_TUCK), SE2Pose(-1.5, 0.0, 0.0))
+    res = p.plan_whole_body(s, g)
+    assert res.success and "base_planning_time_ms" in res.stats
+    base = np.array([[b.x, b.y, b.theta] for b in res.trajectory.base_configs])
+    d = np.diff(base[:, :2], axis=0)
+    heading = np.stack([np.cos(base[:-1, 2]), np.sin(base[:-1, 2])], 1)
+    moving = np.linalg.norm(d, axis=1) > 1e-6
+    backwards = ((d * heading).sum(1) < -1e-6) & moving
+    assert np.linalg.norm(d[backwards], axis=1).sum() < 0.5 * np.linalg.norm(d[moving], axis=1).sum()
 
 
 def test_plan_arm_around_obstacle_is_collision_free(planner):

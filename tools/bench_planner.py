@@ -51,7 +51,25 @@ def main():
         r = planner.plan_arm(free[i], free[i + 1])
         succ += bool(r.success)
         times.append(r.stats.get("planning_time_ms", float("nan")))
-        iters.append(r.stats.get("iterations", float("nan")))
+        iters.append(r.stats.get("planning_iterations", float("nan")))
+    # whole-body planning in the furnished room, all three algorithms (device-resident: no host<->device copies in the loops)
+    import torch
+
+    for algo in ("multilayer_rrtc", "fcit_wb", "rrtc_wb"):
+        p2 = create_planner("fetch", "b200", config=B200PlannerConfig(max_points=1 << 19, whole_body_algorithm=algo, timeout=20.0))
+        p2.update_environment(synth.room_cloud(200_000), SE2Pose(0.0, 0.0, 0.0))
+        _, bases, _ = synth.free_base_configs(p2.world, 24, seed=5, device=torch.device("cuda", 0), base_box=(-3.2, 3.2, -2.2, 2.2))
+        bases = bases.cpu().numpy().astype(np.float64)
+        tuck = np.array([0.0, 1.32, 1.40, -0.2, 1.72, 0.0, 1.66, 0.0])
+        tt, ok_n = [], 0
+        for i in range(0, 24, 2):
+            r = p2.plan_whole_body(WholeBodyConfig(tuck, SE2Pose(*bases[i])), WholeBodyConfig(tuck, SE2Pose(*bases[i + 1])))
+            ok_n += bool(r.success)
+            tt.append(r.stats.get("total_planning_time_ms", float("nan")))
+        out[f"wb_{algo}_success"] = ok_n
+        out[f"wb_{algo}_ms_median"] = float(np.nanmedian(tt))
+        out[f"wb_{algo}_ms_max"] = float(np.nanmax(tt))
+        del p2
     out.update(plan_arm_queries=len(times), plan_arm_success=succ, plan_arm_ms_median=float(np.median(times)),
                plan_arm_ms_max=float(np.max(times)), plan_arm_iterations_median=float(np.median(iters)),
                free_fraction_at_base=float(ok.mean()))

@@ -14,6 +14,8 @@ LIB_PATH = os.environ.get("TYGRIT_B200_LIB") or os.path.join(_HERE, "lib", "libt
 
 TG_N_SPHERES = 111
 TG_N_LINKS = 15
+TG_MAX_OBSTACLES = 64
+TG_MAX_ATTACHED = 64
 
 _lib = None
 
@@ -85,6 +87,29 @@ _SIGS = {
         C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     ),
     "tg_first_valid": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]),
+    "tg_planner_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_void_p, C.c_int, C.c_int]),
+    "tg_planner_destroy": (C.c_int, [C.c_void_p]),
+    "tg_planner_rrt_connect": (
+        C.c_int,
+        [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_uint32, C.c_int, C.c_float, C.c_double,
+         C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p],
+    ),
+    "tg_planner_shortcut": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.c_int, C.c_float, C.c_void_p]),
+    "tg_planner_base_path": (
+        C.c_int,
+        [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_float, C.c_int,
+         C.c_void_p, C.c_int, C.POINTER(C.c_int), C.c_void_p, C.c_void_p],
+    ),
+    "tg_planner_fcit": (
+        C.c_int,
+        [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_uint32, C.c_int,
+         C.c_float, C.c_double, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.c_void_p, C.c_void_p],
+    ),
+    "tg_c5_run": (
+        C.c_int,
+        [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int, C.c_float,
+         C.c_void_p],
+    ),
     "tg_synth_depth": (
         C.c_int,
         [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float, C.c_uint64, C.c_void_p,

@@ -16,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "tygrit_b200", "csrc")
 LIBDIR = os.path.join(ROOT, "tygrit_b200", "lib")
 LIB = os.path.join(LIBDIR, "libtygrit_b200.so")
-SOURCES = ["env.cu", "query.cu", "fkapi.cu", "filter.cu", "host.cu", "synth.cu", "ingest.cu", "occlusion.cu"]
+SOURCES = ["env.cu", "query.cu", "fkapi.cu", "filter.cu", "host.cu", "synth.cu", "ingest.cu", "occlusion.cu", "c5.cu", "planner.cu"]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",

@@ -36,8 +36,16 @@ class B200PlannerConfig(PlannerConfig):
     voxels_per_metre: float = 50.0
     rake: int = 8                 # VAMP's SIMD rake for Fetch (oracle assumption 6)
     resolution: float = 32.0      # samples per unit of configuration-space distance
+    self_collision: bool = True   # VAMP's verdict includes self-collision; pairs = rl/train.py:78-107 SELF_COLLISION_PAIRS
     rrt_batch: int = 512          # candidate extensions validated per iteration
     rrt_range: float = 1.0        # maximum extension length (configuration-space L2)
     rrt_max_iterations: int = 400
-    shortcut_rounds: int = 4
-    seed: int = 0
+    rrt_max_nodes: int = 65536    # capacity of each device-resident tree
+    shortcut_rounds: int = 2      # rounds of all-pairs shortcutting (each: one batched edge check + a DAG shortest path)
+    seed: int = 0                 # offset of the Halton sequence
+    # base layer of multilayer_rrtc (algorithms.py:93-96: HybridAStarConfig.reverse_penalty = 50)
+    reverse_penalty: float = 50.0
+    base_resolution: float = 0.1  # lattice spacing [m] (16 headings)
+    base_turn_cost: float = 0.3   # metres of path cost per radian turned in place
+    base_max_rounds: int = 16     # lazy edge-validation rounds
+    fcit_max_edge: float = 4.0    # the roadmap is complete up to this configuration-space edge length

@@ -144,6 +144,7 @@ struct tg_env {
   size_t blob_capacity;
   cudaArray_t df_array;       // block-linear copy of the distance grid, read through the texture path by phase 1
   cudaTextureObject_t df_tex;
+  cudaSurfaceObject_t df_surf;  // the Z pass of the build writes the array directly
   int arr_n[3];
   uint32_t* cbits;       // coarse occupancy bitmask [gnz][gny][ceil(gnx/32)]
   uint32_t* g2c;         // coarse EDT intermediate, u16 pairs

@@ -99,9 +99,13 @@ k_count(const float* __restrict__ xyz, int n, TgGrid g, uint32_t* __restrict__ o
     if (in_df && in_cells) {
       const unsigned ix = __float_as_uint(fx) - TG_MAGIC_BITS, iy = __float_as_uint(fy) - TG_MAGIC_BITS,
                      iz = __float_as_uint(fz) - TG_MAGIC_BITS;
-      atomicOr(&occ_bits[((size_t)iz * g.ny + iy) * nwx + (ix >> 5)], 1u << (ix & 31));
+      // test before set: bits only ever get set, so a stale read can only cost a redundant atomic (the coarse words are
+      // hit by hundreds of points each)
+      uint32_t* w = &occ_bits[((size_t)iz * g.ny + iy) * nwx + (ix >> 5)];
+      if (!((__ldcg(w) >> (ix & 31)) & 1u)) atomicOr(w, 1u << (ix & 31));
       const unsigned jx = ix / (unsigned)g.cg_r, jy = iy / (unsigned)g.cg_r, jz = iz / (unsigned)g.cg_r;
-      atomicOr(&cbits[(jz * g.gny + jy) * cnwx + (jx >> 5)], 1u << (jx & 31));
+      uint32_t* cw = &cbits[(jz * g.gny + jy) * cnwx + (jx >> 5)];
+      if (!((__ldcg(cw) >> (jx & 31)) & 1u)) atomicOr(cw, 1u << (jx & 31));
       k = (uint32_t)((cz * g.cny + cy) * g.cnx + cx);
       rank[i] = atomicAdd(&cell_count[k], 1u);
     }
@@ -265,15 +269,27 @@ k_edt_xy(const uint32_t* __restrict__ bits, uint32_t* __restrict__ g2w, int nx, 
     tile[r * 32 + lane] = v;
   }
   __syncthreads();
-  if (x >= nxp) return;
   for (int r0 = TGE_T * warp; r0 < TGE_SEG; r0 += TGE_T * (TGE_THREADS / 32)) {
-    if (y0 + r0 >= ny) break;
+    if (y0 + r0 >= ny) break;  // warp-uniform
+    // nothing within W in any of the rows this strip of outputs can see (most of a room's volume): the taps would only
+    // reproduce the sentinel.  One LDS + AND per input row instead of ~10 DPX taps per row.
+    const uint32_t* col = tile + (WB + r0) * 32 + lane;
+    unsigned all = TGE_SENT2;
+#pragma unroll 4
+    for (int j = -WB; j < TGE_T + WB; ++j) all &= col[32 * j];
     unsigned best[TGE_T];
-    tge_taps_blocked<WB>(tile + (WB + r0) * 32 + lane, best);
+    if (__all_sync(0xffffffffu, all == TGE_SENT2)) {
 #pragma unroll
-    for (int t = 0; t < TGE_T; ++t) {
-      const int y = y0 + r0 + t;
-      if (y < ny) g2w[(((size_t)z * ny + y) * nxp + x) >> 1] = best[t];
+      for (int t = 0; t < TGE_T; ++t) best[t] = TGE_SENT2;
+    } else {
+      tge_taps_blocked<WB>(col, best);
+    }
+    if (x < nxp) {
+#pragma unroll
+      for (int t = 0; t < TGE_T; ++t) {
+        const int y = y0 + r0 + t;
+        if (y < ny) g2w[(((size_t)z * ny + y) * nxp + x) >> 1] = best[t];
+      }
     }
   }
 }
@@ -281,7 +297,7 @@ k_edt_xy(const uint32_t* __restrict__ bits, uint32_t* __restrict__ g2w, int nx, 
 // pass Z + quantisation.  grid (ceil(nx/64), ny, ceil(nz/TGE_SEG)).
 template <int WB>
 __global__ void __launch_bounds__(TGE_THREADS)
-k_edt_z(const uint32_t* __restrict__ g2w, uint8_t* __restrict__ df, int nx, int nxp, int ny, int nz, int W) {
+k_edt_z(const uint32_t* __restrict__ g2w, uint8_t* __restrict__ df, cudaSurfaceObject_t surf, int nx, int nxp, int ny, int nz, int W) {
   extern __shared__ uint32_t tile[];  // [TGE_SEG + 2 WB][32] packed pairs
   __shared__ uint8_t lut[1024];       // d2 -> code for d2 < W^2 (W <= 31)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -296,19 +312,35 @@ k_edt_z(const uint32_t* __restrict__ g2w, uint8_t* __restrict__ df, int nx, int 
     tile[r * 32 + lane] = v;
   }
   __syncthreads();
-  if (x >= nx) return;
   for (int r0 = TGE_T * warp; r0 < TGE_SEG; r0 += TGE_T * (TGE_THREADS / 32)) {
-    if (z0 + r0 >= nz) break;
+    if (z0 + r0 >= nz) break;  // warp-uniform
+    const uint32_t* col = tile + (WB + r0) * 32 + lane;
+    unsigned all = TGE_SENT2;  // see k_edt_xy: skip the taps when no input of this strip is below the sentinel
+#pragma unroll 4
+    for (int j = -WB; j < TGE_T + WB; ++j) all &= col[32 * j];
     unsigned best[TGE_T];
-    tge_taps_blocked<WB>(tile + (WB + r0) * 32 + lane, best);
+    if (__all_sync(0xffffffffu, all == TGE_SENT2)) {
 #pragma unroll
-    for (int t = 0; t < TGE_T; ++t) {
-      const int z = z0 + r0 + t;
-      if (z < nz) {
-        const unsigned lo = best[t] & 0xFFFFu, hi = best[t] >> 16;
-        uint8_t* out = df + ((size_t)z * ny + y) * nx + x;
-        out[0] = lo < 1024u ? lut[lo] : (uint8_t)255;
-        if (x + 1 < nx) out[1] = hi < 1024u ? lut[hi] : (uint8_t)255;
+      for (int t = 0; t < TGE_T; ++t) best[t] = TGE_SENT2;
+    } else {
+      tge_taps_blocked<WB>(col, best);
+    }
+    if (x < nx) {
+#pragma unroll
+      for (int t = 0; t < TGE_T; ++t) {
+        const int z = z0 + r0 + t;
+        if (z < nz) {
+          const unsigned lo = best[t] & 0xFFFFu, hi = best[t] >> 16;
+          uint8_t* out = df + ((size_t)z * ny + y) * nx + x;
+          const uint8_t c0 = lo < 1024u ? lut[lo] : (uint8_t)255, c1 = hi < 1024u ? lut[hi] : (uint8_t)255;
+          out[0] = c0;
+          if (x + 1 < nx) out[1] = c1;
+          // the block-linear copy phase 1 reads through the texture path is written here too (no separate 3-D copy)
+          if (surf) {
+            surf3Dwrite(c0, surf, x, y, z);
+            if (x + 1 < nx) surf3Dwrite(c1, surf, x + 1, y, z);
+          }
+        }
       }
     }
   }
@@ -368,12 +400,13 @@ static void tg_launch_edt_coarse(const uint32_t* cbits, uint32_t* g2c, uint8_t* 
 }
 
 template <int WB>
-static void tg_launch_edt(const uint32_t* occ_bits, uint32_t* g2, uint8_t* df, const TgGrid& g, int nxp, int nwx, cudaStream_t st) {
+static void tg_launch_edt(const uint32_t* occ_bits, uint32_t* g2, uint8_t* df, cudaSurfaceObject_t surf, const TgGrid& g, int nxp, int nwx,
+                          cudaStream_t st) {
   const size_t tile_bytes = (size_t)(TGE_SEG + 2 * WB) * 32 * sizeof(uint32_t);
   k_edt_xy<WB><<<dim3(tg_div_up(nxp, 64), tg_div_up(g.ny, TGE_SEG), g.nz), TGE_THREADS, tile_bytes, st>>>(occ_bits, g2, g.nx, nxp, nwx, g.ny,
                                                                                                          g.window);
-  k_edt_z<WB><<<dim3(tg_div_up(g.nx, 64), g.ny, tg_div_up(g.nz, TGE_SEG)), TGE_THREADS, tile_bytes, st>>>(g2, df, g.nx, nxp, g.ny, g.nz,
-                                                                                                        g.window);
+  k_edt_z<WB><<<dim3(tg_div_up(g.nx, 64), g.ny, tg_div_up(g.nz, TGE_SEG)), TGE_THREADS, tile_bytes, st>>>(g2, df, surf, g.nx, nxp, g.ny,
+                                                                                                        g.nz, g.window);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -508,17 +541,18 @@ static void tg_layout(tg_env* env, TgGrid* g, TgHeader* h) {
 // one link (a few cm apart in all three directions) tend to share 32-byte sectors, which a row-major grid only
 // offers along x; the unit also does the index arithmetic and the clamp.  The array is a copy of the blob's linear
 // grid (which stays the thing that is exported / broadcast), refreshed after every build or import.
-static int tg_env_refresh_texture(tg_env* env, cudaStream_t st) {
-  TgGrid& g = env->grid;
+static int tg_env_ensure_array(tg_env* env, TgGrid& g) {
   g.df_tex = 0;
   if (g.empty) return TG_OK;
   if (env->df_array == nullptr || env->arr_n[0] != g.nx || env->arr_n[1] != g.ny || env->arr_n[2] != g.nz) {
     if (env->df_tex) cudaDestroyTextureObject(env->df_tex);
+    if (env->df_surf) cudaDestroySurfaceObject(env->df_surf);
     if (env->df_array) cudaFreeArray(env->df_array);
     env->df_tex = 0;
+    env->df_surf = 0;
     env->df_array = nullptr;
     cudaChannelFormatDesc cd = cudaCreateChannelDesc<unsigned char>();
-    TG_CUDA(cudaMalloc3DArray(&env->df_array, &cd, make_cudaExtent((size_t)g.nx, (size_t)g.ny, (size_t)g.nz)));
+    TG_CUDA(cudaMalloc3DArray(&env->df_array, &cd, make_cudaExtent((size_t)g.nx, (size_t)g.ny, (size_t)g.nz), cudaArraySurfaceLoadStore));
     cudaResourceDesc rd;
     memset(&rd, 0, sizeof(rd));
     rd.resType = cudaResourceTypeArray;
@@ -530,8 +564,19 @@ static int tg_env_refresh_texture(tg_env* env, cudaStream_t st) {
     td.readMode = cudaReadModeElementType;
     td.normalizedCoords = 0;
     TG_CUDA(cudaCreateTextureObject(&env->df_tex, &rd, &td, nullptr));
+    TG_CUDA(cudaCreateSurfaceObject(&env->df_surf, &rd));
     env->arr_n[0] = g.nx; env->arr_n[1] = g.ny; env->arr_n[2] = g.nz;
   }
+  g.df_tex = (unsigned long long)env->df_tex;
+  for (int a = 0; a < 3; ++a) g.tex_bias[a] = 0.5f - (TG_MAGIC - g.bias[a]);  // bias = 2^23 - m
+  return TG_OK;
+}
+
+// import path: the array is filled from the blob's linear grid with one 3-D copy (a build writes it from the Z pass)
+static int tg_env_refresh_texture(tg_env* env, cudaStream_t st) {
+  TgGrid& g = env->grid;
+  const int rc = tg_env_ensure_array(env, g);
+  if (rc || g.empty) return rc;
   cudaMemcpy3DParms cp;
   memset(&cp, 0, sizeof(cp));
   cp.srcPtr = make_cudaPitchedPtr((void*)g.df, (size_t)g.nx, (size_t)g.nx, (size_t)g.ny);
@@ -539,8 +584,6 @@ static int tg_env_refresh_texture(tg_env* env, cudaStream_t st) {
   cp.extent = make_cudaExtent((size_t)g.nx, (size_t)g.ny, (size_t)g.nz);
   cp.kind = cudaMemcpyDeviceToDevice;
   TG_CUDA(cudaMemcpy3DAsync(&cp, st));
-  g.df_tex = (unsigned long long)env->df_tex;
-  for (int a = 0; a < 3; ++a) g.tex_bias[a] = 0.5f - (TG_MAGIC - g.bias[a]);  // bias = 2^23 - m
   return TG_OK;
 }
 
@@ -620,6 +663,7 @@ extern "C" int tg_env_destroy(tg_env* env) {
     cudaFree(env->dev_in[i]); cudaFree(env->dev_out[i]); cudaFree(env->dev_clear[i]);
   }
   if (env->df_tex) cudaDestroyTextureObject(env->df_tex);
+  if (env->df_surf) cudaDestroySurfaceObject(env->df_surf);
   if (env->df_array) cudaFreeArray(env->df_array);
   cudaFree(env->dev_checks);
   cudaFreeHost(env->pin_checks);
@@ -735,6 +779,11 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   uint32_t* cell_start = (uint32_t*)(env->blob + h->off_cells);
   float4* pts = (float4*)(env->blob + h->off_pts);
 
+  {
+    const int rc = tg_env_ensure_array(env, g);  // (re)allocated only when the grid dims change
+    if (rc) return rc;
+  }
+  const cudaSurfaceObject_t surf = env->df_surf;
   const int nwx = (g.nx + 31) / 32, nxp = (g.nx + 1) & ~1;
   uint32_t* occ_bits = (uint32_t*)env->g1;  // occupancy bitmask [nz][ny][nwx]
   TG_CUDA(cudaMemsetAsync(occ_bits, 0, 4 * (size_t)g.nz * g.ny * nwx, st));
@@ -750,13 +799,13 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   k_scan_apply<<<nb, 256, 0, st>>>(env->cell_count, ncell, env->scan_tmp, cell_start);
   k_scatter<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, env->key, env->rank, cell_start, pts);
   switch ((g.window + 3) / 4) {  // window rounded up to a multiple of 4 (W <= 31)
-    case 0: case 1: case 2: tg_launch_edt<8>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
-    case 3: tg_launch_edt<12>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
-    case 4: tg_launch_edt<16>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
-    case 5: tg_launch_edt<20>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
-    case 6: tg_launch_edt<24>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
-    case 7: tg_launch_edt<28>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
-    default: tg_launch_edt<32>(occ_bits, (uint32_t*)env->g2, df, g, nxp, nwx, st); break;
+    case 0: case 1: case 2: tg_launch_edt<8>(occ_bits, (uint32_t*)env->g2, df, surf, g, nxp, nwx, st); break;
+    case 3: tg_launch_edt<12>(occ_bits, (uint32_t*)env->g2, df, surf, g, nxp, nwx, st); break;
+    case 4: tg_launch_edt<16>(occ_bits, (uint32_t*)env->g2, df, surf, g, nxp, nwx, st); break;
+    case 5: tg_launch_edt<20>(occ_bits, (uint32_t*)env->g2, df, surf, g, nxp, nwx, st); break;
+    case 6: tg_launch_edt<24>(occ_bits, (uint32_t*)env->g2, df, surf, g, nxp, nwx, st); break;
+    case 7: tg_launch_edt<28>(occ_bits, (uint32_t*)env->g2, df, surf, g, nxp, nwx, st); break;
+    default: tg_launch_edt<32>(occ_bits, (uint32_t*)env->g2, df, surf, g, nxp, nwx, st); break;
   }
   {  // coarse far-field grid: lower bounds out to ~1.2 m (255 codes of 5 mm)
     const float cell = (float)g.cg_r / g.vpm;
@@ -780,7 +829,7 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   h->grid = g;
   h->thr = env->thr;
   TG_CUDA(cudaMemcpyAsync(env->blob, h, sizeof(TgHeader), cudaMemcpyHostToDevice, st));
-  return tg_env_refresh_texture(env, st);
+  return TG_OK;
 }
 
 extern "C" int tg_env_build_host(tg_env* env, const float* xyz, int64_t n, void* stream_) {

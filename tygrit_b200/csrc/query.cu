@@ -523,8 +523,13 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
       tg_class_clear(cl);
       if (live && !g.empty) {
         const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
+#ifndef TG_EDGE_ROLLED
         if (!fixed_base) tg_stage_a<false>(g, thr, cg0, p, cl);
         if (!cl.collide) tg_stage_b<false, false>(g, thr, cg0, p, cfg + 3, cl);  // derived bounds cost the edge kernel 8 %
+#else  // loops over constant tables instead of the unrolled probes: 18 % less code, but C2 0.66 -> 0.79 ms (r02j): not the default
+        if (!fixed_base) tg_stage_a_rolled(g, thr, p, cl);
+        if (!cl.collide) tg_stage_b_rolled(g, thr, p, cfg + 3, cl);
+#endif
       }
       if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
       hit = __any_sync(0xffffffffu, live && cl.collide);

@@ -338,6 +338,115 @@ __device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, co
 }
 
 // ------------------------------------------------------------------------------------------------
+// ROLLED stage A / stage B for the edge kernel (-DTG_EDGE_ROLLED; a measured variant, NOT the default).  The unrolled
+// forms above are ~60 KB of SASS; in the configuration kernel the 32 warps of a block walk that code together, but in the
+// edge kernel every warp is at its own place in its own edge (ncu, profiles/r02a: stall_no_instruction 4.96 per issue,
+// the largest stall).  Here the same probes are issued from loops over constant-memory tables: six spheres per
+// iteration, one loop body for the seven arm links.  Parity-green, but slower: C2 0.663 -> 0.793 ms, C5 5.56 -> 6.16
+// ms/step - the loop overhead and the serialised link bodies cost more than the instruction fetches save.
+// ------------------------------------------------------------------------------------------------
+__constant__ float TGM_ARM_OFF[7][3] = {
+    {TGM_OFF_SHOULDER_PAN_X, TGM_OFF_SHOULDER_PAN_Y, TGM_OFF_SHOULDER_PAN_Z}, {TGM_OFF_SHOULDER_LIFT_X, TGM_OFF_SHOULDER_LIFT_Y, TGM_OFF_SHOULDER_LIFT_Z},
+    {TGM_OFF_UPPERARM_ROLL_X, TGM_OFF_UPPERARM_ROLL_Y, TGM_OFF_UPPERARM_ROLL_Z}, {TGM_OFF_ELBOW_FLEX_X, TGM_OFF_ELBOW_FLEX_Y, TGM_OFF_ELBOW_FLEX_Z},
+    {TGM_OFF_FOREARM_ROLL_X, TGM_OFF_FOREARM_ROLL_Y, TGM_OFF_FOREARM_ROLL_Z}, {TGM_OFF_WRIST_FLEX_X, TGM_OFF_WRIST_FLEX_Y, TGM_OFF_WRIST_FLEX_Z},
+    {TGM_OFF_WRIST_ROLL_X, TGM_OFF_WRIST_ROLL_Y, TGM_OFF_WRIST_ROLL_Z}};
+__constant__ int TGM_ARM_KIND[7] = {4, 3, 2, 3, 2, 3, 2};            // rotation axis of each arm joint: z, y, x, y, x, y, x
+__constant__ int TGM_ARM_K0[8] = {55, 59, 66, 74, 80, 87, 93, 111};  // kernel-order sphere range of each arm frame
+
+__device__ __forceinline__ void tg_classify_dyn(const TgThr& thr, int k, int code, TgClass& out) {
+  out.collide |= code <= thr.coll_le[k];
+  if (code < thr.free_ge[k]) {
+    const uint32_t bit = 1u << (k & 31);
+    const int w = k >> 5;
+    out.amb[0] |= w == 0 ? bit : 0u;
+    out.amb[1] |= w == 1 ? bit : 0u;
+    out.amb[2] |= w == 2 ? bit : 0u;
+    out.amb[3] |= w == 3 ? bit : 0u;
+  }
+}
+
+// spheres [k0, k1) of a frame given by its voxel-space affine map, six per iteration
+__device__ __forceinline__ void tg_group_rolled(const TgGrid& g, const TgThr& thr, const TgVox& V, int k0, int k1, TgClass& out) {
+  for (int k = k0; k < k1 && !out.collide; k += 6) {
+    int code[6];
+#pragma unroll
+    for (int u = 0; u < 6; ++u) {
+      const int kk = min(k + u, k1 - 1);
+      const float4 l = TGM_K_SPH[kk];
+      const float gx = fmaf(V.G[0], l.x, fmaf(V.G[1], l.y, fmaf(V.G[2], l.z, V.gt[0])));
+      const float gy = fmaf(V.G[3], l.x, fmaf(V.G[4], l.y, fmaf(V.G[5], l.z, V.gt[1])));
+      const float gz = fmaf(V.G[6], l.x, fmaf(V.G[7], l.y, fmaf(V.G[8], l.z, V.gt[2])));
+      code[u] = tg_probe_if(g, k + u < k1, gx, gy, gz, TG_CODE_SKIPPED);
+    }
+#pragma unroll
+    for (int u = 0; u < 6; ++u)
+      if (k + u < k1) tg_classify_dyn(thr, k + u, code[u], out);
+  }
+}
+
+// voxel-space map of a frame whose rotation is the base yaw only, translated by (tx, 0, tz) in base_link
+__device__ __forceinline__ void tg_vox_yaw(const TgGrid& g, const TgPose& p, float tx, float tz, TgVox& V) {
+  V.G[0] = p.cs; V.G[1] = -p.sn; V.G[2] = 0.f;
+  V.G[3] = p.sn; V.G[4] = p.cs;  V.G[5] = 0.f;
+  V.G[6] = 0.f;  V.G[7] = 0.f;   V.G[8] = g.vpm;
+  V.gt[0] = fmaf(p.cs, tx, p.gx0);
+  V.gt[1] = fmaf(p.sn, tx, p.gy0);
+  V.gt[2] = g.vpm * tz;
+}
+
+__device__ __forceinline__ int tg_bound_rolled(const TgGrid& g, const TgVox& V, int b) {
+  const float4 l = TGM_BOUND[b];
+  return tg_probe(g, fmaf(V.G[0], l.x, fmaf(V.G[1], l.y, fmaf(V.G[2], l.z, V.gt[0]))),
+                  fmaf(V.G[3], l.x, fmaf(V.G[4], l.y, fmaf(V.G[5], l.z, V.gt[1]))),
+                  fmaf(V.G[6], l.x, fmaf(V.G[7], l.y, fmaf(V.G[8], l.z, V.gt[2]))));
+}
+
+__device__ __forceinline__ void tg_stage_a_rolled(const TgGrid& g, const TgThr& thr, const TgPose& p, TgClass& out) {
+  TgVox V;
+  tg_vox_yaw(g, p, 0.f, 0.f, V);
+  tg_group_rolled(g, thr, V, 0, 3, out);  // the three big base spheres decide most collisions
+  if (out.collide) return;
+  tg_group_rolled(g, thr, V, 3, 20, out);
+}
+
+__device__ __forceinline__ void tg_stage_b_rolled(const TgGrid& g, const TgThr& thr, const TgPose& p, const float* q, TgClass& out) {
+  const float tz = TGM_OFF_TORSO_Z + q[0];
+  TgVox V;
+  tg_vox_yaw(g, p, TGM_OFF_TORSO_X, tz, V);
+  tg_group_rolled(g, thr, V, 20, 28, out);
+  if (out.collide) return;
+  {
+    const int kb[4] = {28, 33, 44, 55};
+#pragma unroll 1
+    for (int b = 0; b < 3; ++b) {
+      if (tg_bound_rolled(g, V, b) < thr.bound_ge[b]) {
+        tg_group_rolled(g, thr, V, kb[b], kb[b + 1], out);
+        if (out.collide) return;
+      }
+    }
+  }
+  TgFrame F, H;
+  tg_frame_identity(F);
+  F.t[0] = TGM_OFF_TORSO_X;
+  F.t[2] = tz;
+#pragma unroll 1
+  for (int j = 0; j < 7; ++j) {
+    const float ox = TGM_ARM_OFF[j][0], oy = TGM_ARM_OFF[j][1], oz = TGM_ARM_OFF[j][2];
+    switch (TGM_ARM_KIND[j]) {  // the axis must be a compile-time constant inside tg_frame_child (register indexing)
+      case 2: tg_frame_child(F, ox, oy, oz, 2, q[1 + j], H); break;
+      case 3: tg_frame_child(F, ox, oy, oz, 3, q[1 + j], H); break;
+      default: tg_frame_child(F, ox, oy, oz, 4, q[1 + j], H); break;
+    }
+    F = H;
+    tg_vox_frame(g, p, F, V);
+    if (tg_bound_rolled(g, V, 3 + j) < thr.bound_ge[3 + j]) {
+      tg_group_rolled(g, thr, V, TGM_ARM_K0[j], TGM_ARM_K0[j + 1], out);
+      if (out.collide) return;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // exact narrow phase, one lane per sphere (attachments, clearance output): walks the cell rows serially
 // ------------------------------------------------------------------------------------------------
 // true iff some cloud point p has |p - c|^2 <= R^2 (R already includes the point radius).

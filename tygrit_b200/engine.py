@@ -244,6 +244,24 @@ class CollisionWorld:
             )
         return (valid, nchk) if count else valid
 
+    def run_replanning_steps(self, clouds, n_edges: int, steps: int = 100, warmup: int = 3, seed: int = 42,
+                             base_box=(-3.5, 3.5, -2.5, 2.5), rake: int = 8, resolution: float = 32.0) -> dict[str, float]:
+        """BASELINE config 5 as CUDA-graph replays driven from C (``tg_c5_run``): per step fresh device-generated edges,
+        a full rebuild on ``clouds[i % len(clouds)]`` (CUDA (N,3) f32 tensors) and ``n_edges`` edge validations.
+        Needs fixed bounds (:meth:`set_bounds`).  Synchronous."""
+        cl = [_f32c(c, self.device, 3, "cloud") for c in clouds]
+        ptrs = (C.c_void_p * len(cl))(*[c.data_ptr() for c in cl])
+        ns = (C.c_int64 * len(cl))(*[c.shape[0] for c in cl])
+        box = (C.c_float * 4)(*[float(v) for v in base_box])
+        out = (C.c_double * 8)()
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize(self.device)
+            N.check(self._lib.tg_c5_run(self._h, ptrs, ns, len(cl), int(n_edges), int(steps), int(warmup), int(seed), box, int(rake),
+                                        float(resolution), out), "tg_c5_run")
+        k = ("ms_per_step", "build_ms", "valid_fraction", "config_checks_per_step", "graphs", "nodes_per_step_graph", "min_step_ms",
+             "max_step_ms")
+        return dict(zip(k, [float(v) for v in out]))
+
     # ---- host (numpy) variants: the reference-facing path -------------------
     def check_configs_host(self, arm: np.ndarray, base: np.ndarray, out: np.ndarray | None = None,
                            clearance: bool = False):

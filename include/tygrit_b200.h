@@ -251,8 +251,9 @@ int tg_planner_rrt_connect(tg_planner* p, const float* start, const float* goal,
                            int max_iters, uint32_t halton_skip, int rake, float resolution, double timeout_s, float* path_out,
                            int max_path, int* n_path, int* iterations, void* stream);
 /* module.simplify / whole_body_simplify (algorithms.py:51,124): all waypoint pairs validated in one batch, then the
- * shortest path through the valid skips.  path: HOST n x 11 in/out (n <= 128).                                     */
-int tg_planner_shortcut(tg_planner* p, float* path, int* n_io, int rake, float resolution, void* stream);
+ * shortest path through the valid skips; an edge on which the base would drive backwards costs reverse_weight x its
+ * length (1 = plain length).  path: HOST n x 11 in/out (n <= 128).                                                 */
+int tg_planner_shortcut(tg_planner* p, float* path, int* n_io, int rake, float resolution, float reverse_weight, void* stream);
 /* Base layer of multilayer_rrtc (algorithms.py:77-147, HybridAStarConfig.reverse_penalty = 50): SE(2) lattice search
  * (grid `res` metres x 16 headings; forward / backward x reverse_penalty / turn in place), cost-to-go by parallel
  * relaxation, lazy whole-body edge validation with the arm held at arm8.  start, goal: HOST [x, y, theta]; bounds4 HOST
@@ -261,8 +262,9 @@ int tg_planner_base_path(tg_planner* p, const float* start, const float* goal, c
                          float reverse_penalty, float turn_cost, int rake, float resolution, int max_rounds, float* path_out,
                          int max_path, int* n_path, double* stats3, void* stream);
 /* fcit_wb (algorithms.py:155-232: FCITSettings batch_size / max_samples / max_iterations / reverse_weight, XY bounds):
- * lazily evaluated fully connected roadmap over Halton samples.  stats4 HOST {samples drawn, roadmap nodes, lazy rounds,
- * relaxation sweeps} or NULL.                                                                                        */
+ * fully connected roadmap over Halton samples: every pair of valid samples closer than max_edge is validated in ONE
+ * tg_check_edges call, then the cost-to-go is relaxed in parallel.  max_rounds bounds the relaxation sweeps.  stats4 HOST
+ * {samples drawn, roadmap nodes, edges validated, relaxation sweeps} or NULL.                                        */
 int tg_planner_fcit(tg_planner* p, const float* start, const float* goal, const float* lo, const float* hi, int batch_size,
                     int max_samples, int max_rounds, float reverse_weight, float max_edge, uint32_t halton_skip, int rake,
                     float resolution, double timeout_s, float* path_out, int max_path, int* n_path, double* stats4, void* stream);

@@ -152,6 +152,7 @@ struct tg_env {
   uint16_t* g2;          // EDT pass Y output, u16 [nvox]
   uint32_t* cell_count;  // [max_cells + 1]
   uint32_t* rank;        // [max_points]
+  void* sort_tmp;        // float4 [max_points]: points grouped by sort bucket (x, y, z, cell key)
   uint32_t* key;         // [max_points]
   uint32_t* scan_tmp;    // block sums
   float* xyz_stage;      // device staging for host clouds [max_points*3]

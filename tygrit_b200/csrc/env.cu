@@ -200,6 +200,170 @@ k_scatter(const float* __restrict__ xyz, int n, const uint32_t* __restrict__ key
   pts[cell_start[k] + rank[i]] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], 0.f);
 }
 
+// ---- shared-memory staged radix sort of the points by cell key (the default; -DTG_SORT_GLOBAL_ATOMICS = the
+// round-1 pipeline above: one global atomic per point + a 3-kernel scan over all cells) -------------------------------
+// Two-level MSD counting sort.  A BUCKET is a run of 2^cpb_shift consecutive cells (a slab of cell rows):
+//   A  k_sort_hist       per block of 2048 points: voxel / coarse occupancy bits, cell key, bucket histogram in SHARED
+//                        memory, then ONE global atomic per (block, non-empty bucket)
+//   B  k_sort_scan       exclusive scan of the bucket counts (a single block; <= a few thousand buckets)
+//   C  k_sort_partition  per block: shared-memory histogram again, one reservation per (block, bucket), ranks from
+//                        shared-memory atomics, points written as float4 (x, y, z, key) grouped by bucket
+//   D  k_sort_bucket     one block per bucket: histogram of the bucket's cells in shared memory, block scan ->
+//                        cell_start for its cells (no global scan over all cells), second sweep places the points
+#define TGS_CPB_MAX 8192      // cells per bucket: 2048 (8 KB of shared-memory counters in pass D), doubled while the bucket count
+                              // would exceed TGS_MAX_BUCKETS; a power of two (passed as a shift)
+#define TGS_TILE 2048         // points per block in passes A and C
+#define TGS_MAX_BUCKETS 6144  // shared-memory histograms of passes A and C (24 KB / 48 KB)
+
+__device__ __forceinline__ uint32_t tgs_key(const TgGrid& g, float x, float y, float z, bool mark, uint32_t* occ_bits, int nwx, uint32_t* cbits,
+                                            int cnwx) {
+  if (!(isfinite(x) && isfinite(y) && isfinite(z))) return 0xFFFFFFFFu;
+  const float fx = fmaf(x, g.vpm, g.bias[0]), fy = fmaf(y, g.vpm, g.bias[1]), fz = fmaf(z, g.vpm, g.bias[2]);
+  const int cx = (int)floorf(x * g.cpmx) - g.cm[0], cy = (int)floorf(y * g.cpm) - g.cm[1], cz = (int)floorf(z * g.cpm) - g.cm[2];
+  const bool in_df = fx >= TG_MAGIC && fx <= g.hi[0] && fy >= TG_MAGIC && fy <= g.hi[1] && fz >= TG_MAGIC && fz <= g.hi[2];
+  const bool in_cells = cx >= 0 && cx < g.cnx && cy >= 0 && cy < g.cny && cz >= 0 && cz < g.cnz;
+  if (!(in_df && in_cells)) return 0xFFFFFFFFu;
+  if (mark) {
+    const unsigned ix = __float_as_uint(fx) - TG_MAGIC_BITS, iy = __float_as_uint(fy) - TG_MAGIC_BITS, iz = __float_as_uint(fz) - TG_MAGIC_BITS;
+    uint32_t* w = &occ_bits[((size_t)iz * g.ny + iy) * nwx + (ix >> 5)];
+    if (!((__ldcg(w) >> (ix & 31)) & 1u)) atomicOr(w, 1u << (ix & 31));  // test before set: bits only ever get set
+    const unsigned jx = ix / (unsigned)g.cg_r, jy = iy / (unsigned)g.cg_r, jz = iz / (unsigned)g.cg_r;
+    uint32_t* cw = &cbits[(jz * g.gny + jy) * cnwx + (jx >> 5)];
+    if (!((__ldcg(cw) >> (jx & 31)) & 1u)) atomicOr(cw, 1u << (jx & 31));
+  }
+  return (uint32_t)((cz * g.cny + cy) * g.cnx + cx);
+}
+
+__global__ void __launch_bounds__(256)
+k_sort_hist(const float* __restrict__ xyz, int n, TgGrid g, uint32_t* __restrict__ occ_bits, int nwx, uint32_t* __restrict__ cbits, int cnwx,
+            int nbuckets, int cpb_shift, uint32_t* __restrict__ key, uint32_t* __restrict__ bucket_count, int* __restrict__ dropped) {
+  extern __shared__ uint32_t s_hist[];
+  for (int b = threadIdx.x; b < nbuckets; b += 256) s_hist[b] = 0;
+  __syncthreads();
+  int ndrop = 0;
+  for (int j = threadIdx.x; j < TGS_TILE; j += 256) {
+    const int i = blockIdx.x * TGS_TILE + j;
+    if (i >= n) break;
+    const uint32_t k = tgs_key(g, xyz[3 * (size_t)i], xyz[3 * (size_t)i + 1], xyz[3 * (size_t)i + 2], true, occ_bits, nwx, cbits, cnwx);
+    key[i] = k;
+    if (k == 0xFFFFFFFFu) ++ndrop;
+    else atomicAdd(&s_hist[k >> cpb_shift], 1u);
+  }
+  if (ndrop) atomicAdd(dropped, ndrop);
+  __syncthreads();
+  for (int b = threadIdx.x; b < nbuckets; b += 256)
+    if (s_hist[b]) atomicAdd(&bucket_count[b], s_hist[b]);
+}
+
+// exclusive scan of the bucket counts: start[b], start[nbuckets] = kept points; cursor[b] = start[b]
+__global__ void __launch_bounds__(1024) k_sort_scan(const uint32_t* __restrict__ count, int nb, uint32_t* __restrict__ start, uint32_t* __restrict__ cursor) {
+  __shared__ uint32_t warp_tot[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < nb; base += 1024) {
+    const int i = base + threadIdx.x;
+    const uint32_t v = i < nb ? count[i] : 0;
+    uint32_t inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if ((threadIdx.x & 31) >= o) inc += t;
+    }
+    if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      const uint32_t w = warp_tot[threadIdx.x];
+      uint32_t winc = w;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, winc, o);
+        if (threadIdx.x >= o) winc += t;
+      }
+      warp_tot[threadIdx.x] = winc - w;
+    }
+    __syncthreads();
+    const uint32_t excl = carry + warp_tot[threadIdx.x >> 5] + inc - v;
+    if (i < nb) {
+      start[i] = excl;
+      cursor[i] = excl;
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) start[nb] = carry;
+}
+
+__global__ void __launch_bounds__(256)
+k_sort_partition(const float* __restrict__ xyz, int n, const uint32_t* __restrict__ key, int nbuckets, int cpb_shift,
+                 uint32_t* __restrict__ cursor, float4* __restrict__ tmp) {
+  extern __shared__ uint32_t s_mem[];  // [nbuckets] counts -> base offsets, [nbuckets] running ranks
+  uint32_t* s_base = s_mem;
+  uint32_t* s_rank = s_mem + nbuckets;
+  for (int b = threadIdx.x; b < nbuckets; b += 256) s_base[b] = s_rank[b] = 0;
+  __syncthreads();
+  for (int j = threadIdx.x; j < TGS_TILE; j += 256) {
+    const int i = blockIdx.x * TGS_TILE + j;
+    if (i >= n) break;
+    const uint32_t k = key[i];
+    if (k != 0xFFFFFFFFu) atomicAdd(&s_base[k >> cpb_shift], 1u);
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < nbuckets; b += 256)
+    if (s_base[b]) s_base[b] = atomicAdd(&cursor[b], s_base[b]);  // one reservation per (block, bucket)
+  __syncthreads();
+  for (int j = threadIdx.x; j < TGS_TILE; j += 256) {
+    const int i = blockIdx.x * TGS_TILE + j;
+    if (i >= n) break;
+    const uint32_t k = key[i];
+    if (k == 0xFFFFFFFFu) continue;
+    const uint32_t b = k >> cpb_shift;
+    const uint32_t dst = s_base[b] + atomicAdd(&s_rank[b], 1u);
+    tmp[dst] = make_float4(xyz[3 * (size_t)i], xyz[3 * (size_t)i + 1], xyz[3 * (size_t)i + 2], __uint_as_float(k));
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_sort_bucket(const float4* __restrict__ tmp, const uint32_t* __restrict__ bucket_start, int nbuckets, int cpb_shift, int ncell,
+              uint32_t* __restrict__ cell_start, float4* __restrict__ pts) {
+  extern __shared__ uint32_t s_cnt[];  // [cpb]
+  __shared__ uint32_t s_warp[8];
+  const int b = blockIdx.x, cpb = 1 << cpb_shift;
+  const uint32_t p0 = bucket_start[b], p1 = bucket_start[b + 1];
+  const uint32_t c0 = (uint32_t)b << cpb_shift;
+  const int nc = min(cpb, ncell - (int)c0);
+  for (int c = threadIdx.x; c < cpb; c += 256) s_cnt[c] = 0;
+  __syncthreads();
+  for (uint32_t p = p0 + threadIdx.x; p < p1; p += 256) atomicAdd(&s_cnt[__float_as_uint(__ldg(&tmp[p].w)) - c0], 1u);
+  __syncthreads();
+  // block exclusive scan of the cpb counters: cpb / 256 consecutive counters per thread
+  const int per = cpb >> 8;
+  uint32_t sum = 0;
+  for (int j = 0; j < per; ++j) sum += s_cnt[threadIdx.x * per + j];
+  uint32_t inc = sum;
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if ((threadIdx.x & 31) >= o) inc += t;
+  }
+  if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  uint32_t run = p0 + inc - sum;
+  for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) run += s_warp[w];
+  for (int j = 0; j < per; ++j) {
+    const int c = threadIdx.x * per + j;
+    const uint32_t v = s_cnt[c];
+    s_cnt[c] = run;  // becomes the cell's write cursor
+    if (c < nc) cell_start[c0 + c] = run;
+    run += v;
+  }
+  if (b == nbuckets - 1 && threadIdx.x == 0) cell_start[ncell] = p1;
+  __syncthreads();
+  for (uint32_t p = p0 + threadIdx.x; p < p1; p += 256) {
+    const float4 v = __ldg(&tmp[p]);
+    const uint32_t pos = atomicAdd(&s_cnt[__float_as_uint(v.w) - c0], 1u);
+    pts[pos] = make_float4(v.x, v.y, v.z, 0.f);
+  }
+}
+
 // ---- truncated exact EDT --------------------------------------------------------------------------
 // Exact Euclidean distance transform between voxel centres, truncated at W voxels, separable:
 //   X  nearest occupied voxel in the same x-row, straight from the occupancy BITMASK (funnel shift
@@ -620,6 +784,7 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
   TG_CUDA(cudaMalloc(&env->g2, 2 * env->max_voxels + env->max_voxels / 8 + 4096));  // u16 [nz][ny][nxp], nxp = nx rounded up to even
   TG_CUDA(cudaMalloc(&env->cell_count, 4 * (env->max_cells + 1)));
   TG_CUDA(cudaMalloc(&env->rank, 4 * max_points));
+  TG_CUDA(cudaMalloc(&env->sort_tmp, 16 * (size_t)max_points));  // bucket-partitioned points of the staged sort
   TG_CUDA(cudaMalloc(&env->key, 4 * max_points));
   TG_CUDA(cudaMalloc(&env->scan_tmp, 4 * (env->max_cells / SCAN_ITEMS + 2)));
   TG_CUDA(cudaMalloc(&env->bounds_dev, 8 * sizeof(int)));
@@ -652,6 +817,7 @@ extern "C" int tg_env_destroy(tg_env* env) {
   cudaSetDevice(env->device);
   cudaFree(env->cbits); cudaFree(env->g2c);
   cudaFree(env->blob); cudaFree(env->g1); cudaFree(env->g2); cudaFree(env->cell_count);
+  cudaFree(env->sort_tmp);
   cudaFree(env->rank); cudaFree(env->key); cudaFree(env->scan_tmp); cudaFree(env->bounds_dev);
   cudaFree(env->xyz_stage); cudaFree(env->extras_dev); cudaFree(env->items); cudaFree(env->queue_count);
   cudaFree(env->counters_dev);
@@ -789,8 +955,13 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   TG_CUDA(cudaMemsetAsync(occ_bits, 0, 4 * (size_t)g.nz * g.ny * nwx, st));
   const int cnwx = (g.gnx + 31) / 32;
   TG_CUDA(cudaMemsetAsync(env->cbits, 0, 4 * (size_t)g.gnz * g.gny * cnwx, st));
+#ifdef TG_SORT_GLOBAL_ATOMICS
   TG_CUDA(cudaMemsetAsync(env->cell_count, 0, 4 * ((size_t)ncell + 1), st));
+#else
+  TG_CUDA(cudaMemsetAsync(env->cell_count, 0, 4 * (size_t)tg_div_up(ncell, 2048), st));  // bucket counts only (>= the bucket count)
+#endif
   TG_CUDA(cudaMemsetAsync(env->bounds_dev + 6, 0, sizeof(int), st));
+#ifdef TG_SORT_GLOBAL_ATOMICS
   k_count<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, g, occ_bits, nwx, env->cbits, cnwx, env->cell_count, env->key, env->rank,
                                              env->bounds_dev + 6);
   const int nb = tg_div_up(ncell, SCAN_ITEMS);
@@ -798,6 +969,27 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
   k_scan_sums<<<1, 1024, 0, st>>>(env->scan_tmp, nb);
   k_scan_apply<<<nb, 256, 0, st>>>(env->cell_count, ncell, env->scan_tmp, cell_start);
   k_scatter<<<tg_div_up(n, 256), 256, 0, st>>>(xyz, (int)n, env->key, env->rank, cell_start, pts);
+#else
+  {
+    int cpb_shift = 11;  // 2048 cells per bucket: many small blocks in pass D; doubled for very large cell grids
+    while ((1 << cpb_shift) < TGS_CPB_MAX && tg_div_up(ncell, 1 << cpb_shift) > TGS_MAX_BUCKETS) ++cpb_shift;
+    const int nbuckets = tg_div_up(ncell, 1 << cpb_shift);
+    if (nbuckets > TGS_MAX_BUCKETS) {
+      tg_set_error("tg_env_build: %d cells need more sort buckets than supported (coarsen the cells)", ncell);
+      return TG_E_CAPACITY;
+    }
+    uint32_t* bucket_count = env->cell_count;               // [nbuckets] counts, then [nbuckets + 1] starts, then [nbuckets] cursors
+    uint32_t* bucket_start = bucket_count + nbuckets;
+    uint32_t* bucket_cursor = bucket_start + nbuckets + 1;
+    float4* tmp = reinterpret_cast<float4*>(env->sort_tmp);
+    const int tiles = tg_div_up(n, TGS_TILE);
+    k_sort_hist<<<tiles, 256, 4 * nbuckets, st>>>(xyz, (int)n, g, occ_bits, nwx, env->cbits, cnwx, nbuckets, cpb_shift, env->key,
+                                                   bucket_count, env->bounds_dev + 6);
+    k_sort_scan<<<1, 1024, 0, st>>>(bucket_count, nbuckets, bucket_start, bucket_cursor);
+    k_sort_partition<<<tiles, 256, 8 * nbuckets, st>>>(xyz, (int)n, env->key, nbuckets, cpb_shift, bucket_cursor, tmp);
+    k_sort_bucket<<<nbuckets, 256, 4 << cpb_shift, st>>>(tmp, bucket_start, nbuckets, cpb_shift, ncell, cell_start, pts);
+  }
+#endif
   switch ((g.window + 3) / 4) {  // window rounded up to a multiple of 4 (W <= 31)
     case 0: case 1: case 2: tg_launch_edt<8>(occ_bits, (uint32_t*)env->g2, df, surf, g, nxp, nwx, st); break;
     case 3: tg_launch_edt<12>(occ_bits, (uint32_t*)env->g2, df, surf, g, nxp, nwx, st); break;

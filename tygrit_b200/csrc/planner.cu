@@ -295,7 +295,17 @@ __global__ void __launch_bounds__(128) k_sc_pairs(const float* __restrict__ path
   tgp_store_edge(arm0, base0, arm1, base1, tgp_pair_index(i, j, n), a, b);
 }
 
-__global__ void __launch_bounds__(128) k_sc_dp(TgPlanStatus* st, float* path, int n, const uint8_t* __restrict__ valid) {
+// cost of an edge for shortcutting: configuration-space length, times reverse_weight when the base would drive backwards
+// (so that simplification does not undo what the base layer's reverse penalty bought)
+__device__ __forceinline__ float tgp_edge_cost(const float* a, const float* b, float reverse_weight) {
+  const float d = sqrtf(tgp_dist2(a, b));
+  if (reverse_weight == 1.0f) return d;
+  float s, c;
+  __sincosf(a[2], &s, &c);
+  return ((b[0] - a[0]) * c + (b[1] - a[1]) * s) < -1e-3f ? d * reverse_weight : d;
+}
+
+__global__ void __launch_bounds__(128) k_sc_dp(TgPlanStatus* st, float* path, int n, const uint8_t* __restrict__ valid, float reverse_weight) {
   __shared__ float s_cost[128];
   __shared__ int s_prev[128];
   __shared__ float s_path[128 * TGP_STRIDE];
@@ -311,7 +321,7 @@ __global__ void __launch_bounds__(128) k_sc_dp(TgPlanStatus* st, float* path, in
     if (t == 0) s_best = ~0ull;
     __syncthreads();
     if (t < j && (t == j - 1 || valid[tgp_pair_index(t, j, n)])) {  // consecutive waypoints were validated by the planner
-      const float c = s_cost[t] + sqrtf(tgp_dist2(s_path + t * TGP_STRIDE, s_path + j * TGP_STRIDE));
+      const float c = s_cost[t] + tgp_edge_cost(s_path + t * TGP_STRIDE, s_path + j * TGP_STRIDE, reverse_weight);
       atomicMin(&s_best, ((unsigned long long)__float_as_uint(c) << 32) | (unsigned)t);
     }
     __syncthreads();
@@ -495,7 +505,7 @@ extern "C" int tg_planner_rrt_connect(tg_planner* p, const float* start, const f
 
 // Shortcut a path (HOST in/out, n x 11, n <= 128) by validating ALL waypoint pairs in one tg_check_edges call and
 // taking the shortest path through the valid skips.  Consecutive waypoints are taken as valid (the planner's edges).
-extern "C" int tg_planner_shortcut(tg_planner* p, float* path, int* n_io, int rake, float resolution, void* stream_) {
+extern "C" int tg_planner_shortcut(tg_planner* p, float* path, int* n_io, int rake, float resolution, float reverse_weight, void* stream_) {
   TG_CHECK_ARG(p && path && n_io, "tg_planner_shortcut: NULL argument");
   const int n = *n_io;
   if (n <= 2) return TG_OK;
@@ -511,7 +521,7 @@ extern "C" int tg_planner_shortcut(tg_planner* p, float* path, int* n_io, int ra
   const int pairs = n * (n - 1) / 2;
   const int rc = tg_check_edges(p->env, p->sc_arm0, p->sc_base0, p->sc_arm1, p->sc_base1, pairs, rake, resolution, p->sc_valid, nullptr, st);
   if (rc) return rc;
-  k_sc_dp<<<1, 128, 0, st>>>(p->status_dev, p->path, n, p->sc_valid);
+  k_sc_dp<<<1, 128, 0, st>>>(p->status_dev, p->path, n, p->sc_valid, reverse_weight >= 1.0f ? reverse_weight : 1.0f);
   TG_CUDA(cudaGetLastError());
   return tgp_fetch_path(p, path, n, n_io, st);
 }
@@ -812,13 +822,20 @@ extern "C" int tg_planner_base_path(tg_planner* p, const float* start, const flo
 }
 
 // ------------------------------------------------------------------------------------------------
-// fcit_wb: a lazily evaluated, fully connected roadmap (the idea of FCIT*, planning/fetch/algorithms.py:155-232 with
-// batch_size 4096 / max_samples 8192 / reverse_weight 10): Halton samples inside the cloud's XY bounds are validated in
-// one tg_check_configs call; the cost-to-go over the COMPLETE graph of valid samples is relaxed in parallel (one thread
-// per node, all other nodes streamed through shared memory - a min-plus matrix-vector product per sweep); the cheapest
-// path's edges are validated in one tg_check_edges call; refuted edges are struck from the graph and the search repeats.
+// fcit_wb: a FULLY CONNECTED, fully evaluated roadmap (the premise of FCIT*, planning/fetch/algorithms.py:155-232 with
+// batch_size 4096 / max_samples 8192 / reverse_weight 10: edge checks are cheap enough to connect everything): Halton
+// samples inside the cloud's XY bounds are validated in one tg_check_configs call; EVERY pair of valid samples closer
+// than max_edge becomes an edge and all of them (10^5 - 10^6) are validated in ONE tg_check_edges call - a few ms on this
+// machine, where a lazy search needed hundreds of serial rounds in clutter; the cost-to-go over the valid graph is relaxed
+// in parallel (one thread per node, all other nodes streamed through shared memory - a min-plus matrix-vector product
+// per sweep).  A further batch of samples is added (only the new pairs are validated) while the start is unreachable.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_fcit_samples(const float* __restrict__ box, unsigned halton0, int n, float* arm, float* base) {
+// Three of four samples keep the arm on the start configuration, on the goal configuration or on the segment between
+// them (the base is always sampled): a whole-body query mostly moves the BASE, and a roadmap of uniformly random arm
+// postures would make every edge a 5 rad arm swing through the clutter.
+__global__ void __launch_bounds__(256)
+k_fcit_samples(const float* __restrict__ box, const float* __restrict__ ends /* nodes 0 (start) and 1 (goal) */, unsigned halton0, int n,
+               float* arm, float* base) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   float q[TGP_DIM];
@@ -831,6 +848,12 @@ __global__ void __launch_bounds__(256) k_fcit_samples(const float* __restrict__ 
       q[k] = lo + (hi - lo) * tgp_halton(halton0 + (unsigned)i + 1u, TGP_PRIMES[free_dim]);
       ++free_dim;
     }
+  }
+  const unsigned mode = (halton0 + (unsigned)i) & 3u;
+  if (mode) {
+    const float t = mode == 1 ? 0.f : (mode == 2 ? 1.f : tgp_halton(halton0 + (unsigned)i + 1u, 37));
+#pragma unroll
+    for (int k = 3; k < TGP_DIM; ++k) q[k] = ends[k] + t * (ends[TGP_STRIDE + k] - ends[k]);
   }
 #pragma unroll
   for (int k = 0; k < 3; ++k) base[3 * (size_t)i + k] = q[k];
@@ -876,7 +899,7 @@ __device__ __forceinline__ bool tgf_cost(const float* v, const float* u, float r
 }
 
 __global__ void __launch_bounds__(256)
-k_fcit_relax(TgPlanStatus* st, const float* __restrict__ nodes, const int* __restrict__ count, const unsigned* __restrict__ blocked, int words,
+k_fcit_relax(TgPlanStatus* st, const float* __restrict__ nodes, const int* __restrict__ count, const unsigned* __restrict__ ok, int words,
              float reverse_weight, float max_edge, float* dist, int* next) {
   __shared__ float s_nodes[256 * TGP_STRIDE];
   __shared__ float s_dist[256];
@@ -903,7 +926,7 @@ k_fcit_relax(TgPlanStatus* st, const float* __restrict__ nodes, const int* __res
       const float du = s_dist[j];
       if (!(du < best)) continue;  // cannot improve (also skips unreached nodes)
       const int u = u0 + j;
-      if (u == v || (blocked[(size_t)v * words + (u >> 5)] >> (u & 31)) & 1u) continue;
+      if (u == v || !((ok[(size_t)v * words + (u >> 5)] >> (u & 31)) & 1u)) continue;  // only validated edges
       float w;
       if (!tgf_cost(me, s_nodes + j * TGP_STRIDE, reverse_weight, max_edge, &w)) continue;
       if (w + du < best) {
@@ -919,19 +942,46 @@ k_fcit_relax(TgPlanStatus* st, const float* __restrict__ nodes, const int* __res
   }
 }
 
-// path node 0 (start) -> node 1 (goal) along next[]; emits the node list and the edges to validate
-__global__ void k_fcit_walk(TgPlanStatus* st, const float* __restrict__ nodes, const float* __restrict__ dist, const int* __restrict__ next,
-                            int* path_nodes, float* path, float* arm0, float* base0, float* arm1, float* base1, int max_n) {
+// all pairs (i < j, j >= j0) of roadmap nodes closer than max_edge -> edge list (theta of the target unwrapped)
+__global__ void __launch_bounds__(256)
+k_fcit_pairs(const float* __restrict__ nodes, const int* __restrict__ count, int j0, float max_edge, float* arm0, float* base0, float* arm1,
+             float* base1, int2* pair, int* n_edges, int cap) {
+  const int n = *count, j = j0 + blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j >= n || i >= j) return;
+  float a[TGP_STRIDE], b[TGP_STRIDE];
+#pragma unroll
+  for (int k = 0; k < TGP_STRIDE; ++k) {
+    a[k] = nodes[(size_t)i * TGP_STRIDE + k];
+    b[k] = nodes[(size_t)j * TGP_STRIDE + k];
+  }
+  if (tgp_dist2(a, b) > max_edge * max_edge) return;
+  const int e = atomicAdd(n_edges, 1);
+  if (e >= cap) return;  // counted, not stored: the host sees the overflow
+  b[2] = a[2] + tgp_wrap(b[2] - a[2]);
+  tgp_store_edge(arm0, base0, arm1, base1, e, a, b);
+  pair[e] = make_int2(i, j);
+}
+
+__global__ void __launch_bounds__(256)
+k_fcit_mark(const uint8_t* __restrict__ valid, const int2* __restrict__ pair, int E, unsigned* ok, int words) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E || !valid[e]) return;
+  const int2 p = pair[e];
+  atomicOr(&ok[(size_t)p.x * words + (p.y >> 5)], 1u << (p.y & 31));
+  atomicOr(&ok[(size_t)p.y * words + (p.x >> 5)], 1u << (p.x & 31));
+}
+
+// path node 0 (start) -> node 1 (goal) along next[] (every edge of it was validated)
+__global__ void k_fcit_path(TgPlanStatus* st, const float* __restrict__ nodes, const float* __restrict__ dist, const int* __restrict__ next,
+                            float* path, int max_n) {
   st->n_path = 0;
   if (!(dist[0] < 1.0e38f)) return;
   int v = 0, n = 0;
   while (n < max_n) {
-    path_nodes[n] = v;
     for (int k = 0; k < TGP_STRIDE; ++k) path[(size_t)n * TGP_STRIDE + k] = nodes[(size_t)v * TGP_STRIDE + k];
     if (n > 0) {
       float* p = path + (size_t)n * TGP_STRIDE;
       p[2] = p[2 - TGP_STRIDE] + tgp_wrap(p[2] - p[2 - TGP_STRIDE]);
-      tgp_store_edge(arm0, base0, arm1, base1, n - 1, p - TGP_STRIDE, p);
     }
     ++n;
     if (v == 1) {
@@ -943,26 +993,21 @@ __global__ void k_fcit_walk(TgPlanStatus* st, const float* __restrict__ nodes, c
   }
 }
 
-__global__ void __launch_bounds__(128)
-k_fcit_block(TgPlanStatus* st, const int* __restrict__ path_nodes, int n, const uint8_t* __restrict__ valid, unsigned* blocked, int words) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n - 1 || valid[i]) return;
-  const int a = path_nodes[i], b = path_nodes[i + 1];
-  atomicOr(&blocked[(size_t)a * words + (b >> 5)], 1u << (b & 31));
-  atomicOr(&blocked[(size_t)b * words + (a >> 5)], 1u << (a & 31));
-  st->aux = 1;
-}
+__global__ void k_plan_publish(TgPlanStatus* st, const int* value) { st->aux = *value; }
 
 struct TgFcitBuf {
-  int cap, batch;
+  int cap, batch, ecap;
   float *nodes, *dist, *arm, *base;
-  int *next, *count, *path_nodes;
-  unsigned* blocked;
-  uint8_t* valid;
+  int *next, *count, *n_edges;
+  unsigned* ok;
+  uint8_t *valid, *evalid;
+  float *e_arm0, *e_base0, *e_arm1, *e_base1;
+  int2* pair;
 };
+#define TGF_MAX_EDGES (1 << 21)
 
 // start / goal: HOST 11-vectors; lo / hi: HOST sampling box (XY from the cloud bounds, theta, joint limits).
-// stats4 (HOST): samples drawn, roadmap nodes, lazy rounds, relaxation sweeps.  *n_path = 0: no path within the budgets.
+// stats4 (HOST): samples drawn, roadmap nodes, validated edges, relaxation sweeps.  *n_path = 0: no path within the budgets.
 extern "C" int tg_planner_fcit(tg_planner* p, const float* start, const float* goal, const float* lo, const float* hi, int batch_size,
                                int max_samples, int max_rounds, float reverse_weight, float max_edge, uint32_t halton_skip, int rake,
                                float resolution, double timeout_s, float* path_out, int max_path, int* n_path, double* stats4, void* stream_) {
@@ -976,17 +1021,24 @@ extern "C" int tg_planner_fcit(tg_planner* p, const float* start, const float* g
   const int cap = max_samples + 2, words = (cap + 31) / 32;
   if (buf.cap < cap || buf.batch < batch_size) {
     cudaFree(buf.nodes); cudaFree(buf.dist); cudaFree(buf.arm); cudaFree(buf.base); cudaFree(buf.next); cudaFree(buf.count);
-    cudaFree(buf.path_nodes); cudaFree(buf.blocked); cudaFree(buf.valid);
+    cudaFree(buf.n_edges); cudaFree(buf.ok); cudaFree(buf.valid); cudaFree(buf.evalid); cudaFree(buf.e_arm0); cudaFree(buf.e_base0);
+    cudaFree(buf.e_arm1); cudaFree(buf.e_base1); cudaFree(buf.pair);
     memset(&buf, 0, sizeof(buf));
     TG_CUDA(cudaMalloc(&buf.nodes, sizeof(float) * TGP_STRIDE * (size_t)cap));
     TG_CUDA(cudaMalloc(&buf.dist, 4 * (size_t)cap));
     TG_CUDA(cudaMalloc(&buf.next, 4 * (size_t)cap));
     TG_CUDA(cudaMalloc(&buf.count, 4));
-    TG_CUDA(cudaMalloc(&buf.path_nodes, 4 * TGP_MAX_PATH));
-    TG_CUDA(cudaMalloc(&buf.blocked, 4 * (size_t)cap * words));
+    TG_CUDA(cudaMalloc(&buf.n_edges, 4));
+    TG_CUDA(cudaMalloc(&buf.ok, 4 * (size_t)cap * words));
     TG_CUDA(cudaMalloc(&buf.arm, 32 * (size_t)batch_size));
     TG_CUDA(cudaMalloc(&buf.base, 12 * (size_t)batch_size + 16));
     TG_CUDA(cudaMalloc(&buf.valid, (size_t)batch_size));
+    TG_CUDA(cudaMalloc(&buf.evalid, TGF_MAX_EDGES));
+    TG_CUDA(cudaMalloc(&buf.e_arm0, 32 * (size_t)TGF_MAX_EDGES));
+    TG_CUDA(cudaMalloc(&buf.e_arm1, 32 * (size_t)TGF_MAX_EDGES));
+    TG_CUDA(cudaMalloc(&buf.e_base0, 12 * (size_t)TGF_MAX_EDGES + 16));
+    TG_CUDA(cudaMalloc(&buf.e_base1, 12 * (size_t)TGF_MAX_EDGES + 16));
+    TG_CUDA(cudaMalloc(&buf.pair, 8 * (size_t)TGF_MAX_EDGES));
     buf.cap = cap;
     buf.batch = batch_size;
   }
@@ -1002,76 +1054,60 @@ extern "C" int tg_planner_fcit(tg_planner* p, const float* start, const float* g
   TG_CUDA(cudaMemcpyAsync(buf.nodes, row, sizeof(row), cudaMemcpyHostToDevice, st));
   TG_CUDA(cudaMemcpyAsync(buf.count, &two, 4, cudaMemcpyHostToDevice, st));
   TG_CUDA(cudaMemcpyAsync(p->box, box, sizeof(box), cudaMemcpyHostToDevice, st));
-  TG_CUDA(cudaMemsetAsync(buf.blocked, 0, 4 * (size_t)cap * words, st));
+  TG_CUDA(cudaMemsetAsync(buf.ok, 0, 4 * (size_t)cap * words, st));
   TG_CUDA(cudaStreamSynchronize(st));
   const auto t0 = std::chrono::steady_clock::now();
-  int drawn = 0, rounds = 0, sweeps = 0, rc = TG_OK;
+  int drawn = 0, sweeps = 0, rc = TG_OK, n_old = 0;
+  long long edges_total = 0;
   bool found = false;
-  const int max_walk = TGP_MAX_PATH < TGP_SC_MAX ? TGP_MAX_PATH : TGP_SC_MAX;  // path edges are validated in the shortcut workspace
-  while (!found && rounds < max_rounds) {
-    if (drawn < max_samples) {  // one more batch of samples joins the roadmap
-      const int nb = drawn + batch_size <= max_samples ? batch_size : max_samples - drawn;
-      k_fcit_samples<<<tg_div_up(nb, 256), 256, 0, st>>>(p->box, halton_skip + (unsigned)drawn, nb, buf.arm, buf.base);
-      rc = tg_check_configs(p->env, buf.arm, buf.base, nb, buf.valid, nullptr, st);
+  while (!found && drawn < max_samples) {
+    // one more batch of samples joins the roadmap
+    const int nb = drawn + batch_size <= max_samples ? batch_size : max_samples - drawn;
+    k_fcit_samples<<<tg_div_up(nb, 256), 256, 0, st>>>(p->box, buf.nodes, halton_skip + (unsigned)drawn, nb, buf.arm, buf.base);
+    rc = tg_check_configs(p->env, buf.arm, buf.base, nb, buf.valid, nullptr, st);
+    if (rc) return rc;
+    k_fcit_append<<<tg_div_up(nb, 256), 256, 0, st>>>(buf.valid, buf.arm, buf.base, nb, buf.nodes, buf.count, cap);
+    drawn += nb;
+    // every pair that involves a new node, closer than max_edge, becomes a candidate edge; validate them all at once
+    TG_CUDA(cudaMemsetAsync(buf.n_edges, 0, 4, st));
+    k_fcit_pairs<<<dim3(tg_div_up(cap - n_old, 256), cap), 256, 0, st>>>(buf.nodes, buf.count, n_old, max_edge, buf.e_arm0, buf.e_base0,
+                                                                        buf.e_arm1, buf.e_base1, buf.pair, buf.n_edges, TGF_MAX_EDGES);
+    k_plan_publish<<<1, 1, 0, st>>>(p->status_dev, buf.n_edges);
+    TG_CUDA(cudaEventRecord(p->ev, st));
+    TG_CUDA(cudaEventSynchronize(p->ev));
+    int E = p->status->aux;  // a status word in mapped memory, not a copy
+    if (E > TGF_MAX_EDGES) E = TGF_MAX_EDGES;
+    if (E > 0) {
+      rc = tg_check_edges(p->env, buf.e_arm0, buf.e_base0, buf.e_arm1, buf.e_base1, E, rake, resolution, buf.evalid, nullptr, st);
       if (rc) return rc;
-      k_fcit_append<<<tg_div_up(nb, 256), 256, 0, st>>>(buf.valid, buf.arm, buf.base, nb, buf.nodes, buf.count, cap);
-      if (getenv("TG_DEBUG_FCIT")) {
-        cudaStreamSynchronize(st);
-        std::vector<uint8_t> hv(nb);
-        std::vector<float> hb(3 * nb), ha(8 * nb);
-        cudaMemcpy(hv.data(), buf.valid, nb, cudaMemcpyDeviceToHost);
-        cudaMemcpy(hb.data(), buf.base, 12 * nb, cudaMemcpyDeviceToHost);
-        cudaMemcpy(ha.data(), buf.arm, 32 * nb, cudaMemcpyDeviceToHost);
-        int nv = 0, cnt = 0;
-        for (int i = 0; i < nb; ++i) nv += hv[i] != 0;
-        cudaMemcpy(&cnt, buf.count, 4, cudaMemcpyDeviceToHost);
-        fprintf(stderr, "fcit debug: batch %d valid %d count %d err %s | base0 %g %g %g arm0 %g %g %g | base5 %g %g %g\n", nb, nv, cnt,
-                cudaGetErrorString(cudaGetLastError()), hb[0], hb[1], hb[2], ha[0], ha[1], ha[2], hb[15], hb[16], hb[17]);
-      }
-      drawn += nb;
+      k_fcit_mark<<<tg_div_up(E, 256), 256, 0, st>>>(buf.evalid, buf.pair, E, buf.ok, words);
+      edges_total += E;
     }
-    bool reachable = true;
-    while (reachable && !found && rounds < max_rounds) {  // lazy rounds on the current roadmap
-      ++rounds;
-      k_fcit_init<<<tg_div_up(cap, 256), 256, 0, st>>>(buf.dist, buf.next, cap);
-      for (int s = 0; s < 64; ++s) {
-        k_plan_clear<<<1, 1, 0, st>>>(p->status_dev, 1);
-        for (int k = 0; k < 2; ++k)
-          k_fcit_relax<<<tg_div_up(cap, 256), 256, 0, st>>>(p->status_dev, buf.nodes, buf.count, buf.blocked, words, reverse_weight, max_edge,
-                                                           buf.dist, buf.next);
-        sweeps += 2;
-        TG_CUDA(cudaEventRecord(p->ev, st));
-        TG_CUDA(cudaEventSynchronize(p->ev));
-        if (!p->status->changed) break;
-      }
-      k_plan_clear<<<1, 1, 0, st>>>(p->status_dev, 2);
-      k_fcit_walk<<<1, 1, 0, st>>>(p->status_dev, buf.nodes, buf.dist, buf.next, buf.path_nodes, p->path, p->sc_arm0, p->sc_base0, p->sc_arm1,
-                                   p->sc_base1, max_walk);
+    k_plan_publish<<<1, 1, 0, st>>>(p->status_dev, buf.count);
+    // cost-to-go over the validated graph
+    k_fcit_init<<<tg_div_up(cap, 256), 256, 0, st>>>(buf.dist, buf.next, cap);
+    for (int s = 0; s < max_rounds; ++s) {
+      k_plan_clear<<<1, 1, 0, st>>>(p->status_dev, 1);
+      for (int k = 0; k < 2; ++k)
+        k_fcit_relax<<<tg_div_up(cap, 256), 256, 0, st>>>(p->status_dev, buf.nodes, buf.count, buf.ok, words, reverse_weight, max_edge, buf.dist,
+                                                         buf.next);
+      sweeps += 2;
       TG_CUDA(cudaEventRecord(p->ev, st));
       TG_CUDA(cudaEventSynchronize(p->ev));
-      const int nw = p->status->n_path;
-      if (nw < 2) {
-        reachable = false;  // draw more samples (or give up when the budget is spent)
-        break;
-      }
-      rc = tg_check_edges(p->env, p->sc_arm0, p->sc_base0, p->sc_arm1, p->sc_base1, nw - 1, rake, resolution, p->sc_valid, nullptr, st);
-      if (rc) return rc;
-      k_fcit_block<<<tg_div_up(nw - 1, 128), 128, 0, st>>>(p->status_dev, buf.path_nodes, nw, p->sc_valid, buf.blocked, words);
-      TG_CUDA(cudaEventRecord(p->ev, st));
-      TG_CUDA(cudaEventSynchronize(p->ev));
-      found = !p->status->aux;
-      if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > timeout_s) break;
+      if (!p->status->changed) break;
     }
-    if (!found && !reachable && drawn >= max_samples) break;
+    n_old = p->status->aux;  // nodes now in the roadmap: the next batch only pairs its new nodes
+    k_fcit_path<<<1, 1, 0, st>>>(p->status_dev, buf.nodes, buf.dist, buf.next, p->path, TGP_MAX_PATH);
+    TG_CUDA(cudaEventRecord(p->ev, st));
+    TG_CUDA(cudaEventSynchronize(p->ev));
+    found = p->status->n_path >= 2;
     if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > timeout_s) break;
   }
   if (stats4) {
     stats4[0] = drawn;
-    stats4[1] = 0;
-    stats4[2] = rounds;
+    stats4[1] = n_old;
+    stats4[2] = (double)edges_total;
     stats4[3] = sweeps;
-    int cnt = 0;
-    if (cudaMemcpy(&cnt, buf.count, 4, cudaMemcpyDeviceToHost) == cudaSuccess) stats4[1] = cnt;
   }
   TG_CUDA(cudaGetLastError());
   if (!found) return TG_OK;

@@ -232,22 +232,29 @@ __device__ __forceinline__ int tg_bound_code_yaw(const TgGrid& g, const TgThr& t
 }
 // Stage A: the 20 spheres that only depend on the base pose (base_link + torso_fixed), largest first.
 // Most colliding configurations are refuted by the first group of three.
+// Stage A is split in two: the three big base spheres (they refute 65 % of the bench's configurations) and the other 17.
+// The configuration kernel compacts its survivors between the two parts (TG_EARLY_COMPACT), so the 17 smaller spheres
+// already run with full warps; the edge kernel runs both parts back to back.
 template <bool C>
-__device__ __forceinline__ void tg_stage_a(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, TgClass& out) {
+__device__ __forceinline__ void tg_stage_a1(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, TgClass& out) {
   // the largest base sphere alone refutes 55 % of the bench's configurations, the three big ones 65 %
-#ifndef TG_STAGE_A_NOSPLIT
   tg_group_yaw<0, 1, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
   if (out.collide) return;
   tg_group_yaw<1, 3, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
-#else
-  tg_group_yaw<0, 3, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
-#endif
-  if (out.collide) return;
+}
+template <bool C>
+__device__ __forceinline__ void tg_stage_a2(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, TgClass& out) {
   // (enclosing-sphere probes for the torso column and the bumper arc were measured: they rarely prove anything inside
   // a 0.32 m window and cost 1 % more than they save)
   tg_group_yaw<3, 9, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
   if (out.collide) return;
   tg_group_yaw<9, 20, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
+}
+template <bool C>
+__device__ __forceinline__ void tg_stage_a(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, TgClass& out) {
+  tg_stage_a1<C>(g, thr, cg, p, out);
+  if (out.collide) return;
+  tg_stage_a2<C>(g, thr, cg, p, out);
 }
 
 template <int B, bool C>

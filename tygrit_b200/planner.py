@@ -19,7 +19,8 @@ and polls a status word; the finished path is the only device->host copy of a pl
 * ``whole_body_algorithm = "multilayer_rrtc"``: base layer = SE(2) lattice search with ``reverse_penalty = 50``
   (``algorithms.py:93-96``), arm layer = RRT-Connect at the goal base, then whole-body shortcutting; falls back to
   an 11-D RRT-Connect (theta on the shortest arc) when a layer fails.
-* ``whole_body_algorithm = "fcit_wb"``: lazily evaluated fully connected roadmap inside the cloud's XY bounds.
+* ``whole_body_algorithm = "fcit_wb"``: fully connected roadmap inside the cloud's XY bounds, EVERY edge validated in one
+  batched call (10^5-10^6 edges in a few ms).
 Unknown names raise ``ValueError`` (the reference would fail inside ``configure_robot_and_planner_with_kwargs``).
 
 Self-collision: VAMP's ``validate_whole_body_config`` also tests the robot against itself; its pair list is not
@@ -173,10 +174,13 @@ class B200Planner:
         stats = {"planning_time_ms": (time.perf_counter() - t0) * 1e3, "planning_iterations": float(iters)}
         if path is None:
             return PlanResult(success=False, failure=PlannerFailure.NO_PATH_FOUND, stats=stats)
+        raw = path
         if self._config.simplify:
             path = self._shortcut(path)
-        path = self._interpolate_steps(path, self._config.interpolation_steps)
+        path = self._final(path, raw, lambda p: self._interpolate_steps(p, self._config.interpolation_steps), stats)
         stats["planning_time_ms"] = (time.perf_counter() - t0) * 1e3
+        if path is None:
+            return PlanResult(success=False, failure=PlannerFailure.NO_PATH_FOUND, stats=stats)
         # arm-only trajectories carry base [0, 0, 0] for every waypoint (algorithms.py:56-58)
         return PlanResult(success=True, trajectory=make_trajectory(path[:, 3:].tolist(), [[0.0, 0.0, 0.0]] * len(path)),
                           stats=stats)
@@ -208,12 +212,15 @@ class B200Planner:
         stats["total_planning_time_ms"] = (time.perf_counter() - t0) * 1e3
         if path is None:
             return PlanResult(success=False, failure=PlannerFailure.NO_PATH_FOUND, stats=stats)
+        raw = path
         if cfg.simplify or cfg.whole_body_algorithm == "multilayer_rrtc":   # whole_body_simplify is unconditional (algorithms.py:124)
             t1 = time.perf_counter()
-            path = self._shortcut(path)
+            path = self._shortcut(path, cfg.fcit_reverse_weight if cfg.whole_body_algorithm == "fcit_wb" else cfg.reverse_penalty)
             stats["simplification_time_ms"] = (time.perf_counter() - t1) * 1e3
-        path = self._interpolate_density(path, cfg.interpolation_density)
+        path = self._final(path, raw, lambda p: self._interpolate_density(p, cfg.interpolation_density), stats)
         stats["total_planning_time_ms"] = (time.perf_counter() - t0) * 1e3
+        if path is None:
+            return PlanResult(success=False, failure=PlannerFailure.NO_PATH_FOUND, stats=stats)
         return PlanResult(success=True, trajectory=make_trajectory(path[:, 3:].tolist(), path[:, :3].tolist()), stats=stats)
 
     # ------------------------------------------------------------------ #
@@ -353,8 +360,9 @@ class B200Planner:
         path[0], path[-1, :2], path[-1, 3:] = start, goal[:2], goal[3:]      # exact endpoints (the trees hold f32 copies)
         return path, iters.value
 
-    def _shortcut(self, path: np.ndarray) -> np.ndarray:
-        """All waypoint pairs validated in one batch, then the shortest path through the valid skips."""
+    def _shortcut(self, path: np.ndarray, reverse_weight: float = 1.0) -> np.ndarray:
+        """All waypoint pairs validated in one batch, then the shortest path through the valid skips (edges that drive the
+        base backwards cost ``reverse_weight`` x their length)."""
         out = path
         for _ in range(max(1, self._config.shortcut_rounds)):
             if len(out) <= 2:
@@ -367,13 +375,28 @@ class B200Planner:
             buf = np.ascontiguousarray(out, dtype=np.float32)
             n = C.c_int(len(buf))
             N.check(self._lib.tg_planner_shortcut(self._plan, buf.ctypes.data, C.byref(n), int(self._config.rake),
-                                                  float(self._config.resolution), self._stream()), "tg_planner_shortcut")
+                                                  float(self._config.resolution), float(reverse_weight), self._stream()),
+                    "tg_planner_shortcut")
             if n.value >= len(out):
                 break
             new = buf[: n.value].astype(np.float64)
             new[0], new[-1] = out[0], out[-1]
             out = new
         return out
+
+    def _final(self, path: np.ndarray, raw: np.ndarray, interpolate, stats: dict):
+        """Interpolate and re-validate the trajectory that will be returned.  Edge validation samples at a fixed
+        resolution, so the interpolated waypoints' own (shorter, more densely sampled) segments can expose a grazing
+        contact the long edge stepped over; a planner must not hand out a trajectory its own
+        ``check_trajectory_collisions`` rejects.  Falls back to the un-simplified path, then reports failure."""
+        for cand in (path, raw):
+            out = interpolate(cand)
+            if self._edges_ok(out[:-1], out[1:]).all():
+                return out
+            stats["final_check_retries"] = stats.get("final_check_retries", 0.0) + 1.0
+            if cand is raw:
+                break
+        return None
 
     def _edges_ok(self, a: np.ndarray, b: np.ndarray) -> np.ndarray:
         """Validate segments a[i] -> b[i] of 11-vectors [x, y, theta, q0..q7] (theta of b unwrapped relative to a)."""
@@ -396,8 +419,9 @@ class B200Planner:
             out = np.empty((2048, 3), dtype=np.float32)
             n = C.c_int(0)
             st3 = (C.c_double * 3)()
-            N.check(self._lib.tg_planner_base_path(self._plan, _f32(s[:3], 3).ctypes.data, _f32(g[:3], 3).ctypes.data,
-                                                   _f32(s[3:], 8).ctypes.data, bounds.ctypes.data, float(cfg.base_resolution),
+            s3, g3, a8 = _f32(s[:3], 3), _f32(g[:3], 3), _f32(s[3:], 8)    # named: the arrays must outlive the call
+            N.check(self._lib.tg_planner_base_path(self._plan, s3.ctypes.data, g3.ctypes.data,
+                                                   a8.ctypes.data, bounds.ctypes.data, float(cfg.base_resolution),
                                                    float(cfg.reverse_penalty), float(cfg.base_turn_cost), int(cfg.rake), float(cfg.resolution),
                                                    int(cfg.base_max_rounds), out.ctypes.data, 2048, C.byref(n), st3, self._stream()),
                     "tg_planner_base_path")
@@ -432,7 +456,7 @@ class B200Planner:
         return path
 
     def _fcit(self, s: np.ndarray, g: np.ndarray, stats: dict) -> np.ndarray | None:
-        """fcit_wb (algorithms.py:155-232): lazily evaluated fully connected roadmap inside the cloud's XY bounds."""
+        """fcit_wb (algorithms.py:155-232): fully connected, fully validated roadmap inside the cloud's XY bounds."""
         cfg = self._config
         x0, x1, y0, y1 = self._pc_bounds_xy
         x0, x1 = min(x0, s[0], g[0]), max(x1, s[0], g[0])
@@ -443,13 +467,14 @@ class B200Planner:
         n = C.c_int(0)
         st4 = (C.c_double * 4)()
         t0 = time.perf_counter()
-        N.check(self._lib.tg_planner_fcit(self._plan, _f32(s, 11).ctypes.data, _f32(g, 11).ctypes.data, _f32(lo, 11).ctypes.data,
-                                          _f32(hi, 11).ctypes.data, int(cfg.fcit_batch_size), int(max(cfg.fcit_max_samples, cfg.fcit_batch_size)),
+        s32, g32, lo32, hi32 = _f32(s, 11), _f32(g, 11), _f32(lo, 11), _f32(hi, 11)   # named: the arrays must outlive the call
+        N.check(self._lib.tg_planner_fcit(self._plan, s32.ctypes.data, g32.ctypes.data, lo32.ctypes.data,
+                                          hi32.ctypes.data, int(cfg.fcit_batch_size), int(max(cfg.fcit_max_samples, cfg.fcit_batch_size)),
                                           int(cfg.fcit_max_iterations), float(cfg.fcit_reverse_weight), float(cfg.fcit_max_edge),
                                           self._halton_skip & 0x7FFFFFFF, int(cfg.rake), float(cfg.resolution), float(cfg.timeout),
                                           out.ctypes.data, _MAX_PATH, C.byref(n), st4, self._stream()), "tg_planner_fcit")
         stats["arm_planning_time_ms"] = (time.perf_counter() - t0) * 1e3
-        stats["fcit_samples"], stats["fcit_nodes"], stats["fcit_rounds"], stats["fcit_sweeps"] = (float(v) for v in st4)
+        stats["fcit_samples"], stats["fcit_nodes"], stats["fcit_edges_validated"], stats["fcit_sweeps"] = (float(v) for v in st4)
         self._halton_skip += int(st4[0])
         if n.value < 2:
             return None
@@ -457,7 +482,7 @@ class B200Planner:
         path[0], path[-1, :2], path[-1, 3:] = s, g[:2], g[3:]
         if not cfg.fcit_optimize:
             return path
-        return self._shortcut(path)
+        return self._shortcut(path, cfg.fcit_reverse_weight)
 
     @staticmethod
     def _interpolate_steps(path: np.ndarray, steps: int) -> np.ndarray:

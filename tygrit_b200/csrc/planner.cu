@@ -297,12 +297,24 @@ __global__ void __launch_bounds__(128) k_sc_pairs(const float* __restrict__ path
 
 // cost of an edge for shortcutting: configuration-space length, times reverse_weight when the base would drive backwards
 // (so that simplification does not undo what the base layer's reverse penalty bought)
+__device__ __forceinline__ float tgp_reverse_fraction(const float* a, const float* b) {
+  // share of the edge (start, middle, end; theta interpolates linearly along it) on which the base moves against its heading
+  const float dx = b[0] - a[0], dy = b[1] - a[1];
+  if (dx * dx + dy * dy < 1e-10f) return 0.f;
+  const float dth = tgp_wrap(b[2] - a[2]);
+  int n = 0;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    float s, c;
+    __sincosf(a[2] + 0.5f * (float)k * dth, &s, &c);
+    n += (dx * c + dy * s) < -1e-3f;
+  }
+  return (float)n * (1.0f / 3.0f);
+}
 __device__ __forceinline__ float tgp_edge_cost(const float* a, const float* b, float reverse_weight) {
   const float d = sqrtf(tgp_dist2(a, b));
   if (reverse_weight == 1.0f) return d;
-  float s, c;
-  __sincosf(a[2], &s, &c);
-  return ((b[0] - a[0]) * c + (b[1] - a[1]) * s) < -1e-3f ? d * reverse_weight : d;
+  return d * (1.0f + (reverse_weight - 1.0f) * tgp_reverse_fraction(a, b));
 }
 
 __global__ void __launch_bounds__(128) k_sc_dp(TgPlanStatus* st, float* path, int n, const uint8_t* __restrict__ valid, float reverse_weight) {
@@ -891,10 +903,7 @@ __global__ void __launch_bounds__(256) k_fcit_init(float* dist, int* next, int c
 __device__ __forceinline__ bool tgf_cost(const float* v, const float* u, float reverse_weight, float max_edge, float* w) {
   const float d = sqrtf(tgp_dist2(v, u));
   if (d > max_edge) return false;  // the graph is complete up to this edge length
-  float s, c;
-  __sincosf(v[2], &s, &c);
-  const float along = (u[0] - v[0]) * c + (u[1] - v[1]) * s;
-  *w = along < -1e-3f ? d * reverse_weight : d;
+  *w = reverse_weight == 1.0f ? d : d * (1.0f + (reverse_weight - 1.0f) * tgp_reverse_fraction(v, u));
   return true;
 }
 

@@ -1,0 +1,20 @@
+#!/bin/bash
+TAG=${1:-r02q}
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/${TAG}_pytest_gpu.log; tail -5 gpurun_out/${TAG}_pytest_gpu.log | cut -c1-300
+for v in "" warpwalk; do
+  L=$PWD/tygrit_b200/lib/libtygrit_b200${v:+_$v}.so
+  TYGRIT_B200_LIB=$L python bench.py --steps 10 --warmup 3 --no-cpu --no-e2e > gpurun_out/${TAG}_bench_${v:-rowtasks}.json 2> gpurun_out/${TAG}_bench_${v:-rowtasks}.err
+  python - <<PY
+import json
+d=json.load(open("gpurun_out/${TAG}_bench_${v:-rowtasks}.json")); r=d["roofline"]; f=d.get("free_workload",{})
+print("${v:-rowtasks}: value %.4g ms/step %.3f p1 %.4f p2 %.4f | free: %.4g cfg/s %.3f ms" % (d["value"], d["ms_per_step"], r["phase1_avg_launch_ms"], r["phase2_avg_launch_ms"], f.get("value",0), f.get("ms_per_step",0)))
+PY
+done
+python tools/bench_configs.py --only C1,C2,C5 --no-cpu 2>/dev/null | python -c "
+import sys,json
+for l in sys.stdin:
+    d=json.loads(l)
+    if 'uniform' in d: print('C2 uniform %.4f ms rrt_like %.4f ms' % (d['uniform']['ms'], d['rrt_like']['ms']))
+    elif 'device_call_us' in d: print('C1 %.1f us device, %.1f us host' % (d['device_call_us'], d['host_call_us']))
+    else: print('C5 %.3f ms/step build %.0f us' % (d['ms_per_step'], d['build_us']))"

@@ -241,6 +241,7 @@ __global__ void __launch_bounds__(TGR_BLOCK, TGR_MINB) k_resolve(const TgGrid g,
   __shared__ uint16_t s_own[TGR_CAP];
   __shared__ uint32_t s_key[TGR_CAP];
   __shared__ uint16_t s_rest[TGR_CAP];
+  __shared__ uint16_t s_cnt[TGR_CAP + 2];  // row counts -> exclusive row offsets of the selected spheres
   __shared__ unsigned s_nrest;
   __shared__ uint32_t s_best[TGR_ITEMS];
   __shared__ uint32_t s_target[TGR_ITEMS];
@@ -363,6 +364,121 @@ __global__ void __launch_bounds__(TGR_BLOCK, TGR_MINB) k_resolve(const TgGrid g,
         }
         s_key[j] = key;
       }
+#ifdef TGR_ROW_TASKS
+      // MEASURED VARIANT, not the default (-DTGR_ROW_TASKS): the walks as (sphere, cell row) TASKS, one LANE each.  A walked
+      // sphere touches ~6 cell rows with ~8 candidate points each; the default gives every sphere a whole warp (row ranges on
+      // the lanes, a warp prefix sum, a 5-step shuffle search per 32 candidates: ~250 warp instructions per sphere, most of
+      // them bookkeeping).  Here the rows of all selected spheres of the batch are numbered by a block scan and every thread
+      // takes rows: two cell_start loads, then its row's points in sequence - no shuffles, spheres of different items share a
+      // warp.  Parity-green but 2.2 x SLOWER (phase 2 0.82 -> 1.79 ms per 32 Mi configurations, C1 66 -> 152 us, r02q): each
+      // lane streams its own row with 16-byte loads, i.e. 32 sectors per warp load and long divergent loops, where the
+      // warp-wide scan reads 32 consecutive points with one coalesced load.
+      // Wave 0 walks, per open item, the sphere most likely to collide (nine items in ten are collisions); wave 1 the rest.
+      for (int wave = 0; wave < 2; ++wave) {
+        if (wave == 0 && threadIdx.x < TGR_ITEMS) s_best[threadIdx.x] = 0xFFFFFFFFu;
+        if (threadIdx.x == 0) s_nrest = 0;
+        __syncthreads();
+        if (wave == 0) {
+          for (int j = threadIdx.x; j < nw; j += TGR_BLOCK) {
+            const uint32_t key = s_key[j];
+            if (key != 0xFFFFFFFFu && !s_done[s_own[j]]) atomicMin(&s_best[s_own[j]], key);
+          }
+          __syncthreads();
+        }
+        for (int j = threadIdx.x; j < nw; j += TGR_BLOCK) {
+          const uint32_t key = s_key[j];
+          const int own = s_own[j];
+          if (key == 0xFFFFFFFFu || s_done[own] || (wave == 0 && (s_best[own] & 0xFFFFu) != (unsigned)j)) continue;
+          s_key[j] = 0xFFFFFFFFu;  // taken
+          const float4 c = s_sph[j];
+          const TgRows w = tg_rows(g, c.y, c.z, c.w + 1e-4f);
+          if (w.nrows <= 0) continue;
+          const unsigned pos = atomicAdd(&s_nrest, 1u);
+          s_rest[pos] = (uint16_t)j;
+          s_cnt[pos] = (uint16_t)min(w.nrows, 0xFFFF);
+          TG_STAT_LANE(2, 1);
+          TG_STAT_LANE(3, (w.nrows + 31) / 32);
+        }
+        __syncthreads();
+        const int nsel = (int)s_nrest;
+        if (nsel == 0) continue;  // block-uniform
+        // block exclusive scan of the row counts (TGR_CAP / TGR_BLOCK consecutive entries per thread), in place
+        constexpr int PER = TGR_CAP / TGR_BLOCK;
+        static_assert(TGR_CAP % TGR_BLOCK == 0, "the block scan takes TGR_CAP / TGR_BLOCK entries per thread");
+        unsigned loc[PER], sum = 0;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+          const int p = threadIdx.x * PER + k;
+          loc[k] = p < nsel ? (unsigned)s_cnt[p] : 0u;
+          sum += loc[k];
+        }
+        unsigned inc2 = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const unsigned t = __shfl_up_sync(0xffffffffu, inc2, o);
+          if ((int)lane >= o) inc2 += t;
+        }
+        if (lane == 31) s_warp_tot[warp] = (int)inc2;
+        __syncthreads();
+        unsigned run = inc2 - sum, total_rows = 0;
+#pragma unroll
+        for (int w2 = 0; w2 < TGR_BLOCK / 32; ++w2) {
+          if (w2 < (int)warp) run += (unsigned)s_warp_tot[w2];
+          total_rows += (unsigned)s_warp_tot[w2];
+        }
+        const bool fits = total_rows < 0xFFFFu;  // block-uniform; else (huge point radius) fall back to one warp per sphere
+        if (fits) {
+#pragma unroll
+          for (int k = 0; k < PER; ++k) {
+            const int p = threadIdx.x * PER + k;
+            if (p < nsel) s_cnt[p] = (uint16_t)run;
+            run += loc[k];
+          }
+          if (threadIdx.x == 0) s_cnt[nsel] = (uint16_t)total_rows;
+        }
+        __syncthreads();
+        if (fits) {
+          for (unsigned t = threadIdx.x; t < total_rows; t += TGR_BLOCK) {
+            int lo = 0, hi = nsel;  // largest p with s_cnt[p] <= t
+            while (hi - lo > 1) {
+              const int mid = (lo + hi) >> 1;
+              if ((unsigned)s_cnt[mid] <= t) lo = mid; else hi = mid;
+            }
+            const int j = s_rest[lo], own = s_own[j];
+            if (s_done[own]) continue;
+            const float4 c = s_sph[j];
+            const float Re = c.w + 1e-4f;
+            const TgRows w = tg_rows(g, c.y, c.z, Re);
+            uint32_t ps, pe;
+            tg_row_range(g, w, c.x, c.y, c.z, Re, (int)(t - (unsigned)s_cnt[lo]), ps, pe);
+            const float R2 = c.w * c.w;
+            TG_STAT_LANE(9, pe - ps);
+            for (uint32_t q = ps; q < pe; ++q) {
+              const float4 P = __ldg(g.pts + q);
+              const float dx = P.x - c.x, dy = P.y - c.y, dz = P.z - c.z;
+              if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= R2) {
+                TG_STAT_LANE(8, 1);
+                s_done[own] = 1;
+                valid[s_target[own]] = 0;
+                break;
+              }
+              if ((q & 7u) == 7u && s_done[own]) break;  // another row of the item hit meanwhile
+            }
+          }
+        } else {
+          for (int r = (int)warp; r < nsel; r += TGR_BLOCK / 32) {
+            const int j = s_rest[r], own = s_own[j];
+            if (s_done[own]) continue;  // warp-uniform
+            const float4 c = s_sph[j];
+            if (tg_warp_sphere_hits(g, c.x, c.y, c.z, c.w) && lane == 0) {
+              s_done[own] = 1;
+              valid[s_target[own]] = 0;
+            }
+          }
+        }
+        __syncthreads();
+      }
+#else
       // Step 3a: best-first rounds.  Every round picks, per open item, the listed sphere most likely
       // to collide (smallest key) and walks it; nine items in ten are settled within two rounds.
       for (int round = 0; round < TGR_ROUNDS; ++round) {
@@ -454,6 +570,7 @@ __global__ void __launch_bounds__(TGR_BLOCK, TGR_MINB) k_resolve(const TgGrid g,
         }
       }
 #endif
+#endif  // TGR_ROW_TASKS
       __syncthreads();
     }
     __syncthreads();
@@ -553,6 +670,131 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
       atomicAdd(&ctr->definite_collisions, 1ull);
     }
     __syncwarp();
+  }
+  if (n_checks != nullptr && lane == 0 && my_checks) atomicAdd(n_checks, my_checks);
+}
+
+// ------------------------------------------------------------------------------------------------
+// edges, block-synchronised rounds: a MEASURED VARIANT (-DTG_EDGE_SYNC), not the default.  Parity-green but slower than
+// the free-running k_check_edges above: C2 0.665 -> 0.781 ms, C5 5.58 -> 6.51 ms/step with 512-thread blocks (256: 0.774 /
+// 6.35; 1024: 0.840 / 6.86; profiles/r02r_edge_sync_ab.txt) - the warps that wait at the barrier for the one warp of the
+// block that runs a full-length round cost more than the shared instruction fetches save.
+// In k_check_edges every warp walks its own edge at its own pace through a ~140 KB unrolled body, so each warp's
+// instruction stream misses the instruction cache (ncu, profiles/r02a: stall_no_instruction 4.96 per issue, the largest
+// stall).  Here a warp is a small state machine - fetch an edge and run its fixed-base test, or run ONE round of 32
+// samples - and a block barrier sits in front of the round body, so the 16 warps of a block enter stage B together and
+// share its instructions, as the 32 warps of k_check_configs do.  Edges refuted by their base pose (most of a random
+// batch) never reach a round: a warp tries up to 4 edges per iteration before it waits.
+// ------------------------------------------------------------------------------------------------
+#ifndef TGE2_BLOCK
+#define TGE2_BLOCK 512
+#endif
+__global__ void __launch_bounds__(TGE2_BLOCK, 1024 / TGE2_BLOCK)
+k_check_edges_sync(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm0,
+                   const float* __restrict__ base0, const float* __restrict__ arm1, const float* __restrict__ base1, int E, int rake,
+                   float resolution, uint8_t* __restrict__ valid, unsigned long long* __restrict__ n_checks, TgQueue qu,
+                   TgCounters* ctr) {
+  const unsigned lane = threadIdx.x & 31;
+  const int stride = gridDim.x * (TGE2_BLOCK / 32);
+  const TgCoarse cg0 = tg_coarse_init(g, nullptr);  // the edge kernels do not use the coarse grid
+  unsigned long long my_checks = 0;
+  int e_next = blockIdx.x * (TGE2_BLOCK / 32) + (threadIdx.x >> 5);
+  int e = -1, total = 0, rounds = 0, j = 0;
+  float a[11], d[11], inv_total = 0.f;
+  bool active = false, done = false, fixed_base = false;
+  for (;;) {
+    for (int tries = 0; !active && !done && tries < 4; ++tries) {  // warp-uniform
+      if (e_next >= E) {
+        done = true;
+        break;
+      }
+      e = e_next;
+      e_next += stride;
+      a[0] = __ldg(base0 + 3 * (size_t)e); a[1] = __ldg(base0 + 3 * (size_t)e + 1); a[2] = __ldg(base0 + 3 * (size_t)e + 2);
+      d[0] = __ldg(base1 + 3 * (size_t)e); d[1] = __ldg(base1 + 3 * (size_t)e + 1); d[2] = __ldg(base1 + 3 * (size_t)e + 2);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        a[3 + k] = __ldg(arm0 + 8 * (size_t)e + k);
+        d[3 + k] = __ldg(arm1 + 8 * (size_t)e + k);
+      }
+      double s2 = 0.0;  // |b - a|^2 in fp64, order x, y, theta, q0..q7 (matches oracle/collide.py edge_n)
+#pragma unroll
+      for (int k = 0; k < 11; ++k) {
+        const double dk = (double)d[k] - (double)a[k];
+        s2 = s2 + dk * dk;
+        d[k] = d[k] - a[k];
+      }
+      const double nn = ceil(sqrt(s2) * ((double)resolution / (double)rake));
+      const int n = nn < 1.0 ? 1 : (nn > 1.0e6 ? 1000000 : (int)nn);
+      total = rake * n;
+      rounds = (total + 31) >> 5;
+      inv_total = 1.0f / (float)total;
+      if (lane == 0) {
+        my_checks += (unsigned long long)total;
+        valid[e] = 1;  // provisional; cleared below, by an inline resolve, or by phase 2
+      }
+      __syncwarp();
+      bool hit = false;
+      fixed_base = d[0] == 0.f && d[1] == 0.f && d[2] == 0.f;
+      if (fixed_base && !g.empty) {  // the 20 base-pose spheres once per edge, lane k <-> sphere k
+        const TgPose p = tg_pose(g, a[0], a[1], a[2]);
+        bool col = false, am = false;
+        if (lane < 20) {
+          const float4 l = TGM_K_SPH[lane];
+          const float gx = fmaf(p.cs, l.x, fmaf(-p.sn, l.y, p.gx0));
+          const float gy = fmaf(p.sn, l.x, fmaf(p.cs, l.y, p.gy0));
+          const int code = tg_probe(g, gx, gy, g.vpm * l.z);
+          col = code <= thr.coll_le[lane];
+          am = code < thr.free_ge[lane];
+        }
+        hit = __any_sync(0xffffffffu, col);
+        const uint32_t amb0 = __ballot_sync(0xffffffffu, am);
+        const uint32_t m4[4] = {amb0, 0u, 0u, 0u};
+        tg_push_item(g, qu, ctr, lane == 0 && amb0 != 0u && !hit, (uint32_t)e, m4, a, valid);
+      }
+      if (hit) {
+        if (lane == 0) {
+          valid[e] = 0;
+          atomicAdd(&ctr->definite_collisions, 1ull);
+        }
+      } else {
+        active = true;
+        j = 0;
+      }
+    }
+    // every warp of the block is here before any enters the round body: they fetch its instructions together
+    if (!__syncthreads_or((active || !done) ? 1 : 0)) break;
+    if (active) {
+      const int k = (int)lane * rounds + j + 1;
+      const bool live = k <= total;
+      float cfg[11];
+      const float t = (float)k * inv_total;
+#pragma unroll
+      for (int c = 0; c < 11; ++c) cfg[c] = fmaf(t, d[c], a[c]);
+      TgClass cl;
+      tg_class_clear(cl);
+      if (live && !g.empty) {
+        const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
+        if (!fixed_base) tg_stage_a<false>(g, thr, cg0, p, cl);
+        if (!cl.collide) tg_stage_b<false, false>(g, thr, cg0, p, cfg + 3, cl);
+      }
+      if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
+      const bool hit = __any_sync(0xffffffffu, live && cl.collide);
+      if (!hit) {
+        const bool need = live && (cl.amb[0] | cl.amb[1] | cl.amb[2] | cl.amb[3]) != 0u;
+        tg_push_item(g, qu, ctr, need, (uint32_t)e, cl.amb, cfg, valid);
+      }
+      ++j;
+      if (hit) {
+        if (lane == 0) {
+          valid[e] = 0;
+          atomicAdd(&ctr->definite_collisions, 1ull);
+        }
+        active = false;
+      } else if (j >= rounds) {
+        active = false;  // every sample is free or queued: the verdict byte stays 1 unless phase 2 clears it
+      }
+    }
   }
   if (n_checks != nullptr && lane == 0 && my_checks) atomicAdd(n_checks, my_checks);
 }
@@ -820,10 +1062,17 @@ int tg_check_edges_slot(tg_env* env, const float* arm0, const float* base0, cons
   for (int64_t off = 0; off < E; off += chunk) {
     const int ne = (int)((E - off) < chunk ? (E - off) : chunk);
     TG_CUDA(cudaMemsetAsync(qu.count, 0, 2 * sizeof(unsigned), st));
+#ifndef TG_EDGE_SYNC
     const int blocks = min(tg_div_up(ne, TG_BLOCK / 32), env->sm_count * 16);
     k_check_edges<<<blocks, TG_BLOCK, 0, st>>>(env->grid, env->thr, ex, arm0 + 8 * off, base0 + 3 * off, arm1 + 8 * off,
                                                base1 + 3 * off, ne, rake, resolution, valid + off,
                                                (unsigned long long*)n_checks, qu, env->counters_dev);
+#else
+    const int blocks = min(tg_div_up(ne, TGE2_BLOCK / 32), env->sm_count * (1024 / TGE2_BLOCK));
+    k_check_edges_sync<<<blocks, TGE2_BLOCK, 0, st>>>(env->grid, env->thr, ex, arm0 + 8 * off, base0 + 3 * off, arm1 + 8 * off,
+                                                      base1 + 3 * off, ne, rake, resolution, valid + off,
+                                                      (unsigned long long*)n_checks, qu, env->counters_dev);
+#endif
     env->launches += 1;
     if (!env->grid.empty) {
       k_resolve<<<env->sm_count * env->occ_resolve, TGR_BLOCK, 0, st>>>(env->grid, qu, valid + off, env->counters_dev);

@@ -11,8 +11,7 @@ verdict bytes written) over one batch.
 
 N = 1: the step is the check of 64 Mi device-resident configurations.
 N > 1: the step is the whole sharded job — NCCL broadcast of the cloud structure from rank 0, the check of every
-rank's block, and the all-gather of the verdict bytes (chunked: the gather of launch pair i overlaps the kernels of
-pair i + 1) — all inside the timed region.  `value` is the weak-scaling figure (64 Mi configurations per GPU);
+rank's block, and the all-gather of the verdicts, packed to bits (one gather per launch pair) — all inside the timed region.  `value` is the weak-scaling figure (64 Mi configurations per GPU);
 the same line carries `strong` (BASELINE's C4 as stated: 64 Mi configurations in total, split over the N ranks)
 and `replicas_only` (the step without any collective, what round 1 timed).
 
@@ -208,7 +207,7 @@ def main():
                     + (" (base on free floor)" if args.workload == "free" else ""),
         "configs_per_gpu_per_step": args.configs, "cloud_points": CLOUD_POINTS, "point_radius": 0.03,
         "voxels_per_metre": args.vpm, "l2": "inputs (44 B/config = %.1f GB/step) are larger than L2" % (args.configs * 44 / 1e9),
-        "parallelism": f"configs sharded over {world} rank(s); per step: structure NCCL-broadcast from rank 0, verdict bytes all-gathered"
+        "parallelism": f"configs sharded over {world} rank(s); per step: structure NCCL-broadcast from rank 0, verdict bits all-gathered"
                        if world > 1 else "1 rank",
     }
 
@@ -230,6 +229,7 @@ def main():
     import torch
     import torch.distributed as dist
 
+    from tygrit_b200 import engine
     from tygrit_b200.engine import CollisionWorld
     from tygrit_b200.shard import shard_range
 
@@ -278,7 +278,9 @@ def main():
     else:
         arm, base = synth.device_configs(B, seed=42 + rank, device=dev, base_box=BASE_BOX)
     valid = torch.empty(B, dtype=torch.uint8, device=dev)
-    gathered = torch.empty(world * B, dtype=torch.uint8, device=dev) if world > 1 else None   # [chunk][rank][config]
+    # the gather moves verdict BITS (tg_pack_bits: 1/8 of the bytes): [chunk][rank][config / 8]
+    packed = torch.empty((B + 7) // 8 + 8, dtype=torch.uint8, device=dev) if world > 1 else None
+    gathered = torch.empty(world * ((B + 7) // 8 + 8), dtype=torch.uint8, device=dev) if world > 1 else None
 
     def barrier():
         if world > 1:
@@ -286,7 +288,7 @@ def main():
         torch.cuda.synchronize()
 
     def job(arm_t, base_t, valid_t, collectives: bool):
-        """One sharded job on this rank's block: [broadcast structure] -> check -> [all-gather verdict bytes]."""
+        """One sharded job on this rank's block: [broadcast structure] -> check -> [pack + all-gather the verdict bits]."""
         n = arm_t.shape[0]
         if not (collectives and world > 1):
             w.check_configs_into(arm_t, base_t, valid_t)
@@ -298,7 +300,11 @@ def main():
         for off in range(0, n, LAUNCH_CONFIGS):   # one launch pair per chunk; its gather overlaps the next pair's kernels
             m = min(LAUNCH_CONFIGS, n - off)
             w.check_configs_into(arm_t[off:off + m], base_t[off:off + m], valid_t[off:off + m])
-            handles.append(dist.all_gather_into_tensor(gathered[world * off: world * (off + m)], valid_t[off:off + m], async_op=True))
+            o8, m8 = off // 8, (m + 7) // 8
+            engine.pack_verdicts(valid_t[off:off + m], packed[o8:o8 + m8])
+            # 4 MiB per rank and launch pair: 35 us alone.  Not overlapped with the next pair's kernels on purpose: an NCCL kernel
+            # that shares the SMs with the persistent, whole-SM blocks of phase 1 stretched phase 1 by 0.4 ms (r02u)
+            dist.all_gather_into_tensor(gathered[world * o8: world * (o8 + m8)], packed[o8:o8 + m8])
         for h in handles:
             h.wait()
 
@@ -344,7 +350,10 @@ def main():
         # exposed cost of each collective, measured alone on the same buffers
         bc_ms, _ = timed(lambda: dist.broadcast(view, 0), 10)
         m0 = min(B, LAUNCH_CONFIGS)
-        ag_ms, _ = timed(lambda: dist.all_gather_into_tensor(gathered[: world * m0], valid[:m0]), 10)
+        ag_ms, _ = timed(lambda: dist.all_gather_into_tensor(gathered[: world * (m0 // 8)], packed[: m0 // 8]), 10)
+        # the gathered bits of the last job are the verdict bytes: rank r's block, unpacked, equals what rank r computed
+        own = engine.unpack_verdicts(gathered[rank * (m0 // 8): (rank + 1) * (m0 // 8)], m0)
+        assert bool((own == valid[:m0]).all()), "gathered verdict bits differ from the verdict bytes"
         lo, hi = shard_range(B, rank, world)
         s_arm, s_base, s_valid = arm[: hi - lo], base[: hi - lo], valid[: hi - lo]   # this rank's block of the 64 Mi job
         for _ in range(3):
@@ -357,8 +366,9 @@ def main():
             "replicas_only": {"ms_per_step": rep_ms, "value": world * B / (rep_ms * 1e-3),
                               "note": "no collective inside the timed region (what round 1 reported)"},
             "collectives_alone": {"broadcast_ms": bc_ms, "broadcast_bytes": blob_bytes, "broadcast_GBps": blob_bytes / (bc_ms * 1e-3) / 1e9,
-                                  "all_gather_ms": ag_ms, "all_gather_bytes_per_rank": m0,
-                                  "all_gather_GBps_in": (world - 1) * m0 / (ag_ms * 1e-3) / 1e9},
+                                  "all_gather_ms": ag_ms, "all_gather_bytes_per_rank": m0 // 8,
+                                  "all_gather_GBps_in": (world - 1) * (m0 // 8) / (ag_ms * 1e-3) / 1e9,
+                                  "all_gather_payload": "verdict bits (tg_pack_bits), 1 bit per configuration"},
             "ms_per_step_per_rank": ms_per_rank, "clocks_per_rank": all_clocks,
             "strong": {"scaling": "strong", "configs_total": B, "configs_per_gpu": hi - lo, "ms_per_step": st_ms, "value": B / (st_ms * 1e-3),
                        "ms_per_step_per_rank": st_rank, "ms_per_step_without_collectives": st_rep_ms,

@@ -137,6 +137,11 @@ int tg_check_edges(tg_env* env, const float* arm0, const float* base0, const flo
                    const float* base1, int64_t E, int rake, float resolution, uint8_t* valid,
                    int64_t* n_checks, void* stream);
 
+/* Verdict bytes <-> bits (bit i & 7 of byte i / 8 = verdict i): a sharded job gathers 1/8 of the bytes.  All DEVICE;
+ * bits holds ceil(n / 8) bytes.                                                                                   */
+int tg_pack_bits(const uint8_t* valid, int64_t n, uint8_t* bits, void* stream);
+int tg_unpack_bits(const uint8_t* bits, int64_t n, uint8_t* valid, void* stream);
+
 /* HOST-buffer variants (the reference-facing calls: numpy in, numpy out).  They
  * stage through pinned memory in chunks, overlap copies with the kernels, and
  * return after the results are in `valid` (synchronous).                        */

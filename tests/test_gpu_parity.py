@@ -690,3 +690,16 @@ def test_replanning_step_graph_runner():
     w.build(_cuda(clouds_np[0]))
     got = w.check_configs(_cuda(arm), _cuda(base)).cpu().numpy()
     _assert_verdicts(got, cchecker.CCloud(clouds_np[0]).clearance(arm, base, cap=1e-3), "rebuild after graph replays")
+
+
+def test_verdict_bit_packing_round_trip():
+    """tg_pack_bits / tg_unpack_bits (the gather of a sharded job moves verdict bits): ragged sizes, unaligned views."""
+    g = torch.Generator(device="cuda").manual_seed(3)
+    for n in (1, 7, 8, 9, 1000, 65_537, 1 << 20):
+        v = (torch.rand(n + 3, generator=g, device="cuda") < 0.3).to(torch.uint8) * 255   # any non-zero byte is "valid"
+        for view in (v[:n], v[3:3 + n]):                                                   # second view: not 8-byte aligned
+            bits = engine.pack_verdicts(view)
+            assert bits.shape[0] == (n + 7) // 8
+            ref = np.packbits((view.cpu().numpy() != 0).astype(np.uint8), bitorder="little")
+            assert np.array_equal(bits.cpu().numpy(), ref)
+            assert torch.equal(engine.unpack_verdicts(bits, n), (view != 0).to(torch.uint8))

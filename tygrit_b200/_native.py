@@ -54,6 +54,8 @@ _SIGS = {
         [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p,
          C.c_void_p, C.c_void_p],
     ),
+    "tg_pack_bits": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "tg_unpack_bits": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "tg_check_configs_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "tg_check_edges_host": (
         C.c_int,

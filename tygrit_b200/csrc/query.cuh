@@ -619,6 +619,47 @@ __device__ __forceinline__ bool tg_warp_sphere_hits(const TgGrid& g, float cx, f
   return false;
 }
 
+// Warp-cooperative NEAREST point: min over cloud points within Rs of c of |p - c|^2, or Rs^2 when there is none.  Same row
+// ownership and coalesced scan as tg_warp_sphere_hits, with a running minimum instead of the early exit.  All 32 lanes must
+// call it with the same arguments; the result is warp-uniform.
+__device__ __forceinline__ float tg_warp_sphere_min_d2(const TgGrid& g, float cx, float cy, float cz, float Rs) {
+  const unsigned lane = threadIdx.x & 31;
+  const float Re = Rs + 1e-4f;
+  const TgRows w = tg_rows(g, cy, cz, Re);
+  float best = Rs * Rs;
+  for (int r0 = 0; r0 < w.nrows; r0 += 32) {
+    uint32_t s, e;
+    tg_row_range(g, w, cx, cy, cz, Re, r0 + (int)lane, s, e);
+    uint32_t incl = e - s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    for (uint32_t j0 = 0; j0 < total; j0 += 32) {
+      const uint32_t j = j0 + lane;
+      int lo = 0;
+#pragma unroll
+      for (int step = 16; step; step >>= 1) {
+        const uint32_t v = __shfl_sync(0xffffffffu, incl, lo + step - 1);
+        if (v <= j) lo += step;
+      }
+      lo = min(lo, 31);
+      const uint32_t o_incl = __shfl_sync(0xffffffffu, incl, lo);
+      const uint32_t o_e = __shfl_sync(0xffffffffu, e, lo);
+      if (j < total) {
+        const float4 P = __ldg(g.pts + (o_e - (o_incl - j)));
+        const float dx = P.x - cx, dyy = P.y - cy, dzz = P.z - cz;
+        best = fminf(best, fmaf(dx, dx, fmaf(dyy, dyy, dzz * dzz)));
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) best = fminf(best, __shfl_xor_sync(0xffffffffu, best, o));
+  return best;
+}
+
 // Two spheres per warp: lanes 0-15 walk one sphere, lanes 16-31 another (each lane holds ITS half's sphere; `active`
 // is half-uniform).  With the anisotropic cells a sphere touches <= 16 rows almost always, so a half warp is enough
 // for the row lookups, and every instruction of the range arithmetic and of the scan now serves two spheres and two

@@ -311,6 +311,25 @@ def fk_spheres(arm, base, head=None) -> torch.Tensor:
     return out
 
 
+def pack_verdicts(valid: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """(n,) uint8 CUDA verdict bytes -> (ceil(n/8),) uint8 bit mask (bit i & 7 of byte i // 8)."""
+    n = valid.numel()
+    if out is None:
+        out = torch.empty((n + 7) // 8, dtype=torch.uint8, device=valid.device)
+    with torch.cuda.device(valid.device):
+        N.check(N.lib().tg_pack_bits(valid.data_ptr(), n, out.data_ptr(), _stream_ptr(valid.device)), "tg_pack_bits")
+    return out
+
+
+def unpack_verdicts(bits: torch.Tensor, n: int, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Inverse of :func:`pack_verdicts`."""
+    if out is None:
+        out = torch.empty(n, dtype=torch.uint8, device=bits.device)
+    with torch.cuda.device(bits.device):
+        N.check(N.lib().tg_unpack_bits(bits.data_ptr(), int(n), out.data_ptr(), _stream_ptr(bits.device)), "tg_unpack_bits")
+    return out
+
+
 def fk_frames(q10) -> torch.Tensor:
     """Link frames in base_link, (B,15,4,4) CUDA f32."""
     dev = q10.device if isinstance(q10, torch.Tensor) and q10.is_cuda else torch.device("cuda", torch.cuda.current_device())

@@ -584,6 +584,8 @@ __global__ void __launch_bounds__(TGR_BLOCK, TGR_MINB) k_resolve(const TgGrid g,
 // (arm-only planning, plan_arm_rrtc) stage A is the same for every sample: it is evaluated once,
 // with the 20 base-pose spheres spread over the lanes (one probe instruction for the whole edge).
 // ------------------------------------------------------------------------------------------------
+// 72 registers, 7 blocks of 4 warps per SM.  Capping at 64 / 51 registers (8 / 10 blocks) does not pay: C2 0.689 / 0.698 ms
+// against 0.665, C5 5.55 / 5.60 against 5.58 ms/step (profiles/r02w_edge_regs_ab.txt).
 __global__ void __launch_bounds__(TG_BLOCK)
 k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm0,
               const float* __restrict__ base0, const float* __restrict__ arm1, const float* __restrict__ base1, int E, int rake,

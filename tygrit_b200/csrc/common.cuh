@@ -71,6 +71,15 @@ struct TgThr {
   int cbound_ge[16];           // same for the enclosing sphere of a cull group
 };
 
+// Half-resolution distance-bound grid of the CLEARANCE query (built lazily from the fine grid by tg_env_ensure_mid, not part
+// of the blob): one code per block of 2^3 voxels, window 31 blocks (0.69 m at 90 voxels/m, where the fine grid saturates at
+// 0.31 m).  code k < 255: dist(x, cloud) in [k q - slack, (k + 1) q + slack] for every x of the block; 255: >= 255 q - slack.
+struct TgMid {
+  const uint8_t* mg;  // [nz][ny][nx], block (i, j, k) = voxels 2i..2i+1, ...
+  int nx, ny, nz;
+  float q, slack;
+};
+
 struct TgExtras {  // sphere obstacles + end-effector attachment (rarely used; brute force)
   int n_obs;
   int n_att;
@@ -169,6 +178,10 @@ struct tg_env {
   unsigned queue_capacity;
   unsigned queue_limit;  // test hook: 0 = use the whole queue
   int flags;             // TG_FLAG_*: optional terms evaluated by their own kernels after the cloud verdicts
+  uint8_t* mid;          // half-resolution grid of the clearance query (lazy; TgMid)
+  size_t mid_capacity;
+  int mid_valid;         // 0 after every build / import
+  TgMid midg;
   int no_coarse;         // 1 = never use the coarse far-field variant of the configuration kernel (test / tuning hook)
   TgCounters* counters_dev;
   TgCounters* counters_host;  // pinned
@@ -190,7 +203,7 @@ struct tg_env {
   float* pin_small;      // pinned staging of the small-batch host path (one H2D, one D2H per call)
   uint8_t* pin_small_out;
   int sm_count;
-  int occ_configs, occ_resolve;  // resident blocks per SM of the persistent query kernels
+  int occ_configs, occ_resolve, occ_clear;  // resident blocks per SM of the persistent query kernels
 };
 
 int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int64_t B, uint8_t* valid, float* clearance,
@@ -199,5 +212,6 @@ int tg_check_edges_slot(tg_env* env, const float* arm0, const float* base0, cons
                         int rake, float resolution, uint8_t* valid, int64_t* n_checks, void* stream, int slot);
 
 int tg_query_occupancy(tg_env* env);
+int tg_env_ensure_mid(tg_env* env, cudaStream_t st);
 
 static inline int tg_div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

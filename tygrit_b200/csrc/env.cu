@@ -573,6 +573,30 @@ static void tg_launch_edt(const uint32_t* occ_bits, uint32_t* g2, uint8_t* df, c
                                                                                                         g.nz, g.window);
 }
 
+// occupancy bits of the half-resolution grid from the fine codes (code 0 <=> occupied voxel): one thread per block of 2^3
+// voxels, one ballot per 32 blocks.  grid (mnwx, ceil(mny / 8), mnz), block (32, 8).
+__global__ void __launch_bounds__(256)
+k_mid_bits(const uint8_t* __restrict__ df, int nx, int ny, int nz, uint32_t* __restrict__ bits, int mnx, int mny, int mnwx) {
+  const int mx = blockIdx.x * 32 + threadIdx.x, my = blockIdx.y * 8 + threadIdx.y, mz = blockIdx.z;
+  if (my >= mny) return;  // warp-uniform (a warp is one row of threadIdx.y)
+  bool occ = false;
+  if (mx < mnx) {
+#pragma unroll
+    for (int dz = 0; dz < 2; ++dz)
+#pragma unroll
+      for (int dy = 0; dy < 2; ++dy) {
+        const int z = 2 * mz + dz, y = 2 * my + dy;
+        if (z < nz && y < ny) {
+          const uint8_t* row = df + ((size_t)z * ny + y) * nx;
+          occ |= __ldg(row + 2 * mx) == 0;
+          if (2 * mx + 1 < nx) occ |= __ldg(row + 2 * mx + 1) == 0;
+        }
+      }
+  }
+  const unsigned w = __ballot_sync(0xffffffffu, occ);
+  if (threadIdx.x == 0) bits[((size_t)mz * mny + my) * mnwx + blockIdx.x] = w;
+}
+
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
@@ -832,7 +856,7 @@ extern "C" int tg_env_create(tg_env** out, int device, int64_t max_points, float
 extern "C" int tg_env_destroy(tg_env* env) {
   if (!env) return TG_OK;
   cudaSetDevice(env->device);
-  cudaFree(env->cbits); cudaFree(env->g2c);
+  cudaFree(env->cbits); cudaFree(env->g2c); cudaFree(env->mid);
   cudaFree(env->blob); cudaFree(env->g1); cudaFree(env->g2); cudaFree(env->cell_count);
   cudaFree(env->sort_tmp);
   cudaFree(env->rank); cudaFree(env->key); cudaFree(env->scan_tmp); cudaFree(env->bounds_dev);
@@ -1035,9 +1059,40 @@ extern "C" int tg_env_build(tg_env* env, const float* xyz, int64_t n, void* stre
 
   tg_compute_thresholds(g, &env->thr);
   env->grid = g;
+  env->mid_valid = 0;
   h->grid = g;
   h->thr = env->thr;
   TG_CUDA(cudaMemcpyAsync(env->blob, h, sizeof(TgHeader), cudaMemcpyHostToDevice, st));
+  return TG_OK;
+}
+
+// The half-resolution grid of the clearance query, (re)built on `st` when the structure changed since the last call.
+// Scratch: g1 (occupancy bits) and g2 (pass-Y output) of the build.
+int tg_env_ensure_mid(tg_env* env, cudaStream_t st) {
+  if (env->mid_valid || env->grid.empty) return TG_OK;
+  const TgGrid& g = env->grid;
+  TgGrid gm = g;
+  gm.nx = (g.nx + 1) / 2; gm.ny = (g.ny + 1) / 2; gm.nz = (g.nz + 1) / 2;
+  gm.window = 31;
+  const size_t need = (size_t)gm.nx * gm.ny * gm.nz;
+  if (need > env->mid_capacity) {
+    if (env->mid) TG_CUDA(cudaFree(env->mid));
+    env->mid = nullptr;
+    env->mid_capacity = 0;
+    TG_CUDA(cudaMalloc(&env->mid, need + need / 8 + 4096));
+    env->mid_capacity = need + need / 8 + 4096;
+  }
+  const int nwx = (gm.nx + 31) / 32, nxp = (gm.nx + 1) & ~1;
+  uint32_t* bits = (uint32_t*)env->g1;
+  k_mid_bits<<<dim3(nwx, tg_div_up(gm.ny, 8), gm.nz), dim3(32, 8), 0, st>>>(g.df, g.nx, g.ny, g.nz, bits, gm.nx, gm.ny, nwx);
+  tg_launch_edt<32>(bits, (uint32_t*)env->g2, env->mid, 0, gm, nxp, nwx, st);
+  TG_CUDA(cudaGetLastError());
+  env->launches += 3;
+  env->midg.mg = env->mid;
+  env->midg.nx = gm.nx; env->midg.ny = gm.ny; env->midg.nz = gm.nz;
+  env->midg.q = (float)((31.0 * 2.0 / (double)g.vpm) / 255.0);
+  env->midg.slack = (float)(2.0 * sqrt(3.0) / (double)g.vpm + kEpsFp + 0.02 * env->midg.q);
+  env->mid_valid = 1;
   return TG_OK;
 }
 
@@ -1132,6 +1187,7 @@ extern "C" int tg_env_import(tg_env* env, const void* blob, size_t bytes, void* 
     g.cg = env->blob + h->off_cg;
   }
   env->grid = g;
+  env->mid_valid = 0;
   env->thr = h->thr;
   env->r_pt = g.r_pt;
   return tg_env_refresh_texture(env, st);

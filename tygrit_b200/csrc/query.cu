@@ -801,14 +801,49 @@ k_check_edges_sync(const TgGrid g, const TgThr thr, const TgExtras* __restrict__
   if (n_checks != nullptr && lane == 0 && my_checks) atomicAdd(n_checks, my_checks);
 }
 
+__device__ __forceinline__ int tgc_f2ord(float f) {
+  const int i = __float_as_int(f);
+  return i >= 0 ? i : i ^ 0x7FFFFFFF;
+}
+__device__ __forceinline__ float tgc_ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7FFFFFFF); }
+
+// Distance code of a sphere centre (grid coordinates) for the clearance query, 10 bits:
+//   < 255: fine code; 255 + m: fine code saturated, half-resolution code m (TgMid); + 512: the centre is outside that grid.
+__device__ __forceinline__ unsigned tgc_code(const TgGrid& g, const TgMid& m, float gx, float gy, float gz) {
+  const unsigned code = (unsigned)tg_probe(g, gx, gy, gz);
+  if (code < 255u || m.mg == nullptr) return code;
+  const int fx = __float2int_rd(gx + g.tex_bias[0]), fy = __float2int_rd(gy + g.tex_bias[1]), fz = __float2int_rd(gz + g.tex_bias[2]);
+  const bool outside = fx < 0 || fy < 0 || fz < 0 || fx >= g.nx || fy >= g.ny || fz >= g.nz;
+  const int ix = min(max(fx, 0), g.nx - 1) >> 1, iy = min(max(fy, 0), g.ny - 1) >> 1, iz = min(max(fz, 0), g.nz - 1) >> 1;
+  return 255u + (unsigned)__ldg(m.mg + ((size_t)iz * m.ny + iy) * m.nx + ix) + (outside ? 512u : 0u);
+}
+// interval [lo, hi] that contains (distance from the centre to the cloud) - R; hi = +inf when nothing bounds it from above.
+// Outside the grid the (clamped) code still bounds from below: the cloud lies inside the box and clamping is the projection.
+__device__ __forceinline__ void tgc_interval(const TgGrid& g, const TgMid& m, unsigned v, float R, float& lo, float& hi) {
+  const bool outside = v >= 512u;
+  v &= 511u;
+  if (v < 255u) {
+    lo = (float)v * g.q - g.slack - R;
+    hi = (float)(v + 1u) * g.q + g.slack - R;
+    return;
+  }
+  lo = 255.0f * g.q - g.slack - R;
+  hi = __int_as_float(0x7f800000);
+  if (m.mg != nullptr) {
+    const unsigned c = v - 255u;
+    lo = fmaxf(lo, (float)c * m.q - m.slack - R);
+    if (c < 255u && !outside) hi = (float)(c + 1u) * m.q + m.slack - R;
+  }
+}
+
 // clearance (optional output of tg_check_configs): exact, clipped at TG_CLEARANCE_CAP.
-// Two passes per configuration (one lane each).  Pass 1 reads, for every sphere, the fine distance code (and the coarse
-// far-field code where the fine one is saturated) and turns it into an interval [lo, hi] that contains the sphere's own
-// clearance; the smallest hi bounds the answer from above.  Pass 2 walks cloud points only for the spheres whose lo is
-// below that bound, and only out to the bound - a handful of spheres and a few cells each, instead of every sphere out
-// to the 0.25 m cap (the first version: 3.1e7 configurations/s).
+// Lane-per-configuration form (used when obstacle / attachment spheres are set; the block-cooperative kernel below is the
+// default).  Pass 1 reads, for every sphere, the fine distance code (the half-resolution code where the fine one is
+// saturated) = an interval [lo, hi] that contains the sphere's own clearance; the smallest hi bounds the answer from above.
+// The sphere that owns it is searched first, then only the spheres whose lo is below the (now mostly exact) bound, and only
+// out to that bound.
 __global__ void __launch_bounds__(TG_BLOCK)
-k_clearance(const TgGrid g, const TgExtras* __restrict__ ex, const float* __restrict__ arm, const float* __restrict__ base,
+k_clearance(const TgGrid g, const TgMid m, const TgExtras* __restrict__ ex, const float* __restrict__ arm, const float* __restrict__ base,
             int B, float* __restrict__ clearance, int flags) {
   const int i = blockIdx.x * TG_BLOCK + threadIdx.x;
   if (i >= B) return;
@@ -822,10 +857,12 @@ k_clearance(const TgGrid g, const TgExtras* __restrict__ ex, const float* __rest
   float best = TG_CLEARANCE_CAP;
   const int n_att = ex ? ex->n_att : 0, n_obs = ex ? ex->n_obs : 0;
   const int ns = TG_N_SPHERES + n_att;
-  float lo_k[TG_N_SPHERES + TG_MAX_ATTACHED];
+  uint16_t code_k[TG_N_SPHERES + TG_MAX_ATTACHED];
+  int first = -1;
   for (int pass = 0; pass < 2; ++pass) {
-    for (int k = 0; k < ns; ++k) {
-      if (pass == 1 && !(lo_k[k] < best)) continue;
+    for (int kk = (pass == 0 ? 0 : -1); kk < ns; ++kk) {
+      const int k = kk < 0 ? first : kk;  // pass 1 starts with the owner of the smallest hi
+      if (k < 0 || (pass == 1 && kk == first)) continue;
       float4 c;
       if (k < TG_N_SPHERES) c = tg_sphere_world(L, b, k);
       else {
@@ -834,30 +871,31 @@ k_clearance(const TgGrid g, const TgExtras* __restrict__ ex, const float* __rest
         const float3 pw = tg_to_world(b, pb.x, pb.y, pb.z);
         c = make_float4(pw.x, pw.y, pw.z, l.w);
       }
+      const float R = c.w + g.r_pt;
       if (pass == 0) {
-        float lo = TG_CLEARANCE_CAP;  // no cloud: nothing below the cap
         if (!g.empty) {
-          const float R = c.w + g.r_pt;
-          const float gx = c.x * g.vpm, gy = c.y * g.vpm, gz = c.z * g.vpm;
-          const int code = tg_probe(g, gx, gy, gz);
-          lo = (float)code * g.q - g.slack - R;
-          if (code < 255) {
-            best = fminf(best, (float)(code + 1) * g.q + g.slack - R);  // the sphere is at most this clear
-          } else {  // saturated: the coarse far-field grid (global copy) may prove more
-            const int ix = min(max(__float2int_rd((gx + g.tex_bias[0]) * g.cg_inv_r), 0), g.gnx - 1);
-            const int iy = min(max(__float2int_rd((gy + g.tex_bias[1]) * g.cg_inv_r), 0), g.gny - 1);
-            const int iz = min(max(__float2int_rd((gz + g.tex_bias[2]) * g.cg_inv_r), 0), g.gnz - 1);
-            lo = fmaxf(lo, (float)__ldg(g.cg + ((size_t)iz * g.gny + iy) * g.gnx + ix) * g.cg_q - R);
+          const unsigned v = tgc_code(g, m, c.x * g.vpm, c.y * g.vpm, c.z * g.vpm);
+          code_k[k] = (uint16_t)v;
+          float lo, hi;
+          tgc_interval(g, m, v, R, lo, hi);
+          if (hi < best) {
+            best = hi;
+            first = k;
           }
         }
-        lo_k[k] = lo;
         for (int o = 0; o < n_obs; ++o) {  // sphere obstacles: exact, cheap
           const float4 ob = ex->obs[o];
           const float dx = c.x - ob.x, dy = c.y - ob.y, dz = c.z - ob.z;
-          best = fminf(best, sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) - c.w - ob.w);
+          const float d = sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) - c.w - ob.w;
+          if (d < best) {
+            best = d;
+            first = -1;  // exact already
+          }
         }
       } else {
-        best = fminf(best, tg_sphere_clearance(g, c.x, c.y, c.z, c.w + g.r_pt, fmaxf(best, 0.f)));
+        float lo, hi;
+        tgc_interval(g, m, code_k[k], R, lo, hi);
+        if (lo < best && R + best > 0.f) best = fminf(best, tg_sphere_clearance(g, c.x, c.y, c.z, R, best));
       }
     }
     if (g.empty) break;
@@ -866,39 +904,58 @@ k_clearance(const TgGrid g, const TgExtras* __restrict__ ex, const float* __rest
   clearance[i] = best;
 }
 
-// clearance, block-cooperative (-DTG_CLEARANCE_BLOCK; a MEASURED VARIANT, not the default: 4.4e7 configurations/s against
-// 5.1e7 for the kernel above on the bench batch - the time goes into the large-radius searches of configurations whose
-// clearance is near the 0.25 m cap, which neither form avoids): 64 configurations per block iteration.  (1) two warps run the FK, one lane per configuration, and leave the 15 WORLD link frames in shared memory;
-// (2) all 128 threads take (configuration, sphere) pairs: centre from the frame, fine distance code (coarse far-field code
-// where it is saturated) -> an interval [lo, hi] around the sphere's own clearance, smallest hi per configuration by a
-// shared-memory atomic; (3) the pairs whose lo is below that bound are the candidates; (4) ONE WARP per candidate finds
-// the nearest cloud point within the bound with the coalesced row scan of the narrow phase (tg_warp_sphere_min_d2) and
-// lowers the configuration's minimum.  The lane-per-configuration kernel above walks its candidates' points serially.
+// clearance, block-cooperative (the default when there are no obstacle / attachment spheres): 64 configurations per block
+// iteration.
+//  (1) the first 64 threads run the FK, one lane per configuration, and leave the 15 WORLD link frames in shared memory;
+//  (2) all threads take (configuration, sphere) pairs: centre from the frame, fine distance code - where that is
+//      saturated (centre farther than ~0.3 m) the code of the half-resolution grid (TgMid, out to ~0.7 m) - kept as 10 bits
+//      per pair; a code is an interval [lo, hi] around the sphere's own clearance, the smallest hi per configuration
+//      (shared-memory atomic) bounds the answer from above;
+//  (3) round A: the sphere that owns that smallest hi is searched first, by a GROUP of TGCL_G lanes (nearest cloud point
+//      within the bound, coalesced row scan of the narrow phase, centre-out, the radius shrinking as points are found): the
+//      bound becomes exact for that sphere, which is the arg-min most of the time;
+//  (4) round B: the other pairs whose lo is still below the bound are the candidates (2.8 per configuration on the bench
+//      batch), one group each, the bound shrinking as they finish.
+// Without the half-resolution grid a configuration whose big spheres sit between 0.3 m and the 0.25 m cap + radius from
+// the cloud had no upper bound and searched out to 0.52 m: 80 % of the time of the first version (r02t: 5.1e7 /s).
+// Measured (r02x, 4 Mi configurations of the bench batch): lane kernel + half-resolution grid 1.60e8 /s; this kernel with
+// groups of 4 / 8 / 16 / 32 lanes at 256 threads 1.45 / 1.75 / 1.88 / 1.73e8; 512 threads, groups of 8 / 16: 2.42 / 2.65e8 /s;
+// 1024 threads, groups of 8: 1.76e8 (profiles/r02x_clearance.txt).
 #define TGCL_CFGS 64
-#define TGCL_BLOCK 128
+#ifndef TGCL_BLOCK
+#define TGCL_BLOCK 512
+#endif
+#ifndef TGCL_G
+#define TGCL_G 16  // lanes per nearest-point search
+#endif
 struct TgClearSmem {
-  float fr[TGCL_CFGS][TGM_N_LINKS][12];   // world frames: rotation row-major, translation
-  float lo[TGCL_CFGS * TG_N_SPHERES];
-  int best[TGCL_CFGS];                    // ordered-int image of the running minimum
+  float fr[TGCL_CFGS][TGM_N_LINKS][12];       // world frames: rotation row-major, translation
+  uint16_t code[TGCL_CFGS * TG_N_SPHERES];    // tgc_code
   uint16_t cand[TGCL_CFGS * TG_N_SPHERES];
+  int best[TGCL_CFGS];                        // ordered-int image of the running minimum
+  int first[TGCL_CFGS];                       // pair that owns the smallest hi (-1: none)
+  float4 sph[TG_N_SPHERES];                   // link-frame centre, radius (indexed per lane: shared, not constant memory)
+  uint8_t link[TG_N_SPHERES + 1];
   unsigned ncand;
 };
-__device__ __forceinline__ int tgc_f2ord(float f) {
-  const int i = __float_as_int(f);
-  return i >= 0 ? i : i ^ 0x7FFFFFFF;
-}
-__device__ __forceinline__ float tgc_ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7FFFFFFF); }
 
 __global__ void __launch_bounds__(TGCL_BLOCK)
-k_clearance_block(const TgGrid g, const float* __restrict__ arm, const float* __restrict__ base, int B, float* __restrict__ clearance) {
+k_clearance_block(const TgGrid g, const TgMid m, const float* __restrict__ arm, const float* __restrict__ base, int B,
+                  float* __restrict__ clearance) {
   extern __shared__ __align__(16) unsigned char tgcl_smem[];
   TgClearSmem& sm = *reinterpret_cast<TgClearSmem*>(tgcl_smem);
-  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NG = TGCL_BLOCK / TGCL_G;  // search groups per block
+  const int gi = threadIdx.x / TGCL_G, gl = threadIdx.x & (TGCL_G - 1);
+  for (int j = threadIdx.x; j < TG_N_SPHERES; j += TGCL_BLOCK) {
+    sm.sph[j] = TGM_SPH_REF[j];
+    sm.link[j] = TGM_SPH_LINK[j];
+  }
   for (int c0 = blockIdx.x * TGCL_CFGS; c0 < B; c0 += gridDim.x * TGCL_CFGS) {
     const int nc = min(TGCL_CFGS, B - c0);
     if (threadIdx.x < TGCL_CFGS) {
       const int c = threadIdx.x;
       sm.best[c] = tgc_f2ord(TG_CLEARANCE_CAP);
+      sm.first[c] = -1;
       if (c < nc) {
         const int i = c0 + c;
         float q10[10];
@@ -925,47 +982,78 @@ k_clearance_block(const TgGrid g, const float* __restrict__ arm, const float* __
     if (threadIdx.x == 0) sm.ncand = 0;
     __syncthreads();
     const int npairs = nc * TG_N_SPHERES;
-    for (int p = threadIdx.x; p < npairs; p += TGCL_BLOCK) {
+    for (int p = threadIdx.x; p < npairs; p += TGCL_BLOCK) {  // (2) codes and the smallest upper bound
       const int c = p / TG_N_SPHERES, j = p - c * TG_N_SPHERES;
-      const float4 l = TGM_SPH_REF[j];
-      const float* f = sm.fr[c][TGM_SPH_LINK[j]];
+      const float4 l = sm.sph[j];
+      const float* f = sm.fr[c][sm.link[j]];
       const float cx = fmaf(f[0], l.x, fmaf(f[1], l.y, fmaf(f[2], l.z, f[9])));
       const float cy = fmaf(f[3], l.x, fmaf(f[4], l.y, fmaf(f[5], l.z, f[10])));
       const float cz = fmaf(f[6], l.x, fmaf(f[7], l.y, fmaf(f[8], l.z, f[11])));
-      const float R = l.w + g.r_pt;
-      const float gx = cx * g.vpm, gy = cy * g.vpm, gz = cz * g.vpm;
-      const int code = tg_probe(g, gx, gy, gz);
-      float lo = (float)code * g.q - g.slack - R;
-      if (code < 255) {
-        atomicMin(&sm.best[c], tgc_f2ord((float)(code + 1) * g.q + g.slack - R));
-      } else {
-        const int ix = min(max(__float2int_rd((gx + g.tex_bias[0]) * g.cg_inv_r), 0), g.gnx - 1);
-        const int iy = min(max(__float2int_rd((gy + g.tex_bias[1]) * g.cg_inv_r), 0), g.gny - 1);
-        const int iz = min(max(__float2int_rd((gz + g.tex_bias[2]) * g.cg_inv_r), 0), g.gnz - 1);
-        lo = fmaxf(lo, (float)__ldg(g.cg + ((size_t)iz * g.gny + iy) * g.gnx + ix) * g.cg_q - R);
-      }
-      sm.lo[p] = lo;
+      const unsigned v = tgc_code(g, m, cx * g.vpm, cy * g.vpm, cz * g.vpm);
+      sm.code[p] = (uint16_t)v;
+      float lo, hi;
+      tgc_interval(g, m, v, l.w + g.r_pt, lo, hi);
+      if (hi < TG_CLEARANCE_CAP) atomicMin(&sm.best[c], tgc_f2ord(hi));
     }
     __syncthreads();
-    for (int p = threadIdx.x; p < npairs; p += TGCL_BLOCK) {
-      const int c = p / TG_N_SPHERES;
-      if (sm.lo[p] < tgc_ord2f(sm.best[c])) sm.cand[atomicAdd(&sm.ncand, 1u)] = (uint16_t)p;
+    for (int p = threadIdx.x; p < npairs; p += TGCL_BLOCK) {  // who owns it (any of several equal ones)
+      const int c = p / TG_N_SPHERES, j = p - c * TG_N_SPHERES;
+      float lo, hi;
+      tgc_interval(g, m, sm.code[p], sm.sph[j].w + g.r_pt, lo, hi);
+      if (tgc_f2ord(hi) == sm.best[c]) sm.first[c] = p;
+    }
+    __syncthreads();
+    for (int cb = 0; cb < nc; cb += NG) {  // (3) round A: one search per configuration, one group of TGCL_G lanes each
+      const int c = cb + gi;
+      const int p = c < nc ? sm.first[c] : -1;
+      bool act = p >= 0;
+      float cx = 0.f, cy = 0.f, cz = 0.f, R = 0.f, Rs = 0.f;
+      if (act) {
+        const int j = p - c * TG_N_SPHERES;
+        const float4 l = sm.sph[j];
+        const float* f = sm.fr[c][sm.link[j]];
+        cx = fmaf(f[0], l.x, fmaf(f[1], l.y, fmaf(f[2], l.z, f[9])));
+        cy = fmaf(f[3], l.x, fmaf(f[4], l.y, fmaf(f[5], l.z, f[10])));
+        cz = fmaf(f[6], l.x, fmaf(f[7], l.y, fmaf(f[8], l.z, f[11])));
+        R = l.w + g.r_pt;
+        Rs = R + tgc_ord2f(sm.best[c]);
+        act = Rs > 0.f;
+      }
+      const float d2 = tg_group_sphere_min_d2<TGCL_G>(g, act, cx, cy, cz, act ? Rs : 0.f);
+      if (act && gl == 0 && d2 < Rs * Rs) sm.best[c] = tgc_f2ord(sqrtf(d2) - R);  // only a point that was really found
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < npairs; p += TGCL_BLOCK) {  // (4) the pairs the bound does not exclude
+      const int c = p / TG_N_SPHERES, j = p - c * TG_N_SPHERES;
+      float lo, hi;
+      tgc_interval(g, m, sm.code[p], sm.sph[j].w + g.r_pt, lo, hi);
+      if (p != sm.first[c] && lo < tgc_ord2f(sm.best[c])) sm.cand[atomicAdd(&sm.ncand, 1u)] = (uint16_t)p;
     }
     __syncthreads();
     const int ncand = (int)sm.ncand;
-    for (int k = (int)warp; k < ncand; k += TGCL_BLOCK / 32) {
-      const int p = sm.cand[k], c = p / TG_N_SPHERES, j = p - c * TG_N_SPHERES;
-      const float best = tgc_ord2f(sm.best[c]);  // may have been lowered by another warp meanwhile (only helps)
-      if (!(sm.lo[p] < best)) continue;          // warp-uniform
-      const float4 l = TGM_SPH_REF[j];
-      const float* f = sm.fr[c][TGM_SPH_LINK[j]];
-      const float cx = fmaf(f[0], l.x, fmaf(f[1], l.y, fmaf(f[2], l.z, f[9])));
-      const float cy = fmaf(f[3], l.x, fmaf(f[4], l.y, fmaf(f[5], l.z, f[10])));
-      const float cz = fmaf(f[6], l.x, fmaf(f[7], l.y, fmaf(f[8], l.z, f[11])));
-      const float R = l.w + g.r_pt;
-      const float Rs = R + fmaxf(best, 0.f);
-      const float d2 = tg_warp_sphere_min_d2(g, cx, cy, cz, Rs);
-      if (lane == 0 && d2 < Rs * Rs) atomicMin(&sm.best[c], tgc_f2ord(sqrtf(d2) - R));  // only a point that was really found
+    for (int kb = 0; kb < ncand; kb += NG) {
+      const int k = kb + gi;
+      bool act = k < ncand;
+      float cx = 0.f, cy = 0.f, cz = 0.f, R = 0.f, Rs = 0.f;
+      int c = 0;
+      if (act) {
+        const int p = sm.cand[k];
+        c = p / TG_N_SPHERES;
+        const int j = p - c * TG_N_SPHERES;
+        const float best = tgc_ord2f(sm.best[c]);  // may have been lowered by another group meanwhile (only helps)
+        const float4 l = sm.sph[j];
+        R = l.w + g.r_pt;
+        float lo, hi;
+        tgc_interval(g, m, sm.code[p], R, lo, hi);
+        Rs = R + best;
+        act = lo < best && Rs > 0.f;
+        const float* f = sm.fr[c][sm.link[j]];
+        cx = fmaf(f[0], l.x, fmaf(f[1], l.y, fmaf(f[2], l.z, f[9])));
+        cy = fmaf(f[3], l.x, fmaf(f[4], l.y, fmaf(f[5], l.z, f[10])));
+        cz = fmaf(f[6], l.x, fmaf(f[7], l.y, fmaf(f[8], l.z, f[11])));
+      }
+      const float d2 = tg_group_sphere_min_d2<TGCL_G>(g, act, cx, cy, cz, act ? Rs : 0.f);
+      if (act && gl == 0 && d2 < Rs * Rs) atomicMin(&sm.best[c], tgc_f2ord(sqrtf(d2) - R));
     }
     __syncthreads();
     if (threadIdx.x < nc) clearance[c0 + threadIdx.x] = tgc_ord2f(sm.best[threadIdx.x]);
@@ -1050,8 +1138,11 @@ int tg_query_occupancy(tg_env* env) {
                                                         sizeof(TgRing<TGC_BLOCK_PLAIN>)));
   TG_CUDA(cudaFuncSetAttribute(k_clearance_block, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TgClearSmem)));
   TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_resolve, TGR_BLOCK, 0));
+  int c = 0;
+  TG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c, k_clearance_block, TGCL_BLOCK, sizeof(TgClearSmem)));
   env->occ_configs = a > 0 ? a : 1;
   env->occ_resolve = b > 0 ? b : 1;
+  env->occ_clear = c > 0 ? c : 1;
   return TG_OK;
 }
 
@@ -1147,17 +1238,22 @@ int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int6
       env->launches += 1;
     }
     if (clearance) {
-#ifdef TG_CLEARANCE_BLOCK  // measured variant: 4.4e7 against 5.1e7 configurations/s for the lane-per-configuration kernel (r02t)
+      if (!env->grid.empty) {
+        const int rc = tg_env_ensure_mid(env, st);  // the half-resolution grid, once per structure
+        if (rc) return rc;
+      }
+      const TgMid mid = env->grid.empty ? TgMid{nullptr, 0, 0, 0, 0.f, 0.f} : env->midg;
+#ifndef TG_CLEARANCE_LANES  // -DTG_CLEARANCE_LANES: the lane-per-configuration kernel for everything (A/B)
       if (ex == nullptr && !env->grid.empty) {  // no obstacle / attachment spheres: the block-cooperative kernel
-        k_clearance_block<<<min(tg_div_up(nb, TGCL_CFGS), env->sm_count * 2), TGCL_BLOCK, sizeof(TgClearSmem), st>>>(
-            env->grid, arm + 8 * off, base + 3 * off, nb, clearance + off);
+        k_clearance_block<<<min(tg_div_up(nb, TGCL_CFGS), env->sm_count * env->occ_clear), TGCL_BLOCK, sizeof(TgClearSmem), st>>>(
+            env->grid, mid, arm + 8 * off, base + 3 * off, nb, clearance + off);
         if (env->flags & TG_FLAG_SELF) {
           k_self_clearance<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(arm + 8 * off, nb, clearance + off);
           env->launches += 1;
         }
       } else
 #endif
-        k_clearance<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(env->grid, ex, arm + 8 * off, base + 3 * off, nb, clearance + off, env->flags);
+        k_clearance<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(env->grid, mid, ex, arm + 8 * off, base + 3 * off, nb, clearance + off, env->flags);
       env->launches += 1;
     }
   }

@@ -490,6 +490,7 @@ __device__ inline bool tg_sphere_hits_cloud(const TgGrid& g, float cx, float cy,
 }
 
 // min over cloud points of (|p - c| - R), clipped to `limit` (search radius R + limit).
+// `limit` may be negative (a deeper penetration is already known): R + limit must be positive.
 __device__ inline float tg_sphere_clearance(const TgGrid& g, float cx, float cy, float cz, float R, float limit) {
   const float Rs = R + limit + 1e-4f;
   float best2 = (R + limit) * (R + limit);
@@ -519,7 +520,7 @@ __device__ inline float tg_sphere_clearance(const TgGrid& g, float cx, float cy,
       }
     }
   }
-  return sqrtf(best2) - R;
+  return best2 < (R + limit) * (R + limit) ? sqrtf(best2) - R : limit;  // only a point that was really found changes the bound
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -619,44 +620,88 @@ __device__ __forceinline__ bool tg_warp_sphere_hits(const TgGrid& g, float cx, f
   return false;
 }
 
-// Warp-cooperative NEAREST point: min over cloud points within Rs of c of |p - c|^2, or Rs^2 when there is none.  Same row
-// ownership and coalesced scan as tg_warp_sphere_hits, with a running minimum instead of the early exit.  All 32 lanes must
-// call it with the same arguments; the result is warp-uniform.
-__device__ __forceinline__ float tg_warp_sphere_min_d2(const TgGrid& g, float cx, float cy, float cz, float Rs) {
-  const unsigned lane = threadIdx.x & 31;
-  const float Re = Rs + 1e-4f;
-  const TgRows w = tg_rows(g, cy, cz, Re);
+// Cooperative NEAREST point: min over cloud points within Rs of c of |p - c|^2, or Rs^2 when there is none, by a GROUP of G
+// lanes (G = 4, 8, 16 or 32; 32 / G independent searches per warp, each group with its own arguments; `active` = false makes
+// a group idle).  Same row ownership and coalesced scan as tg_warp_sphere_hits, with a running minimum instead of the early
+// exit; z slices are visited centre-out (jc, jc + 1, jc - 1, ...): the nearest point is usually found in the first batch of
+// rows, after which the radius - and with it the chords of the remaining rows, most of them then empty - shrinks.
+// The searches are latency-bound (cell_start -> points, one dependent round trip per batch of rows), so what pays is
+// searches in flight, not lanes per search.  Every lane of the warp must call it; loops run until the slowest group of the
+// warp is done; the result is group-uniform.
+template <int G>
+__device__ __forceinline__ float tg_group_sphere_min_d2(const TgGrid& g, bool active, float cx, float cy, float cz, float Rs) {
+  const unsigned full = 0xffffffffu;
+  const int gl = (int)(threadIdx.x & (G - 1));
+  float Re = Rs + 1e-4f;
+  TgRows w = tg_rows(g, cy, cz, Re);
+  if (!active) w.nrows = 0;
   float best = Rs * Rs;
-  for (int r0 = 0; r0 < w.nrows; r0 += 32) {
-    uint32_t s, e;
-    tg_row_range(g, w, cx, cy, cz, Re, r0 + (int)lane, s, e);
+  const int nz = w.ny > 0 ? w.nrows / w.ny : 0;
+  const int jc = min(max((int)floorf(cz * g.cpm) - g.cm[2] - w.z0, 0), max(nz - 1, 0));
+  const int mside = min(jc, nz - 1 - jc);
+  const float inv = 1.0f / g.cpm;
+  for (int r0 = 0; __any_sync(full, r0 < w.nrows); r0 += G) {
+    uint32_t s = 0, e = 0;
+    const int r = r0 + gl;
+    if (r < w.nrows) {
+      const int k = (int)(((float)r + 0.5f) * w.inv_ny);  // r / ny (exact: r < 2^20)
+      const int jz = k <= 2 * mside ? jc + ((k & 1) ? (k + 1) / 2 : -(k / 2)) : (jc > nz - 1 - jc ? nz - 1 - k : k);
+      const int iz = w.z0 + jz, iy = w.y0 + (r - k * w.ny);
+      const float zlo = (float)(iz + g.cm[2]) * inv, ylo = (float)(iy + g.cm[1]) * inv;
+      const float dz = fmaxf(0.f, fmaxf(zlo - cz, cz - (zlo + inv)));
+      const float dy = fmaxf(0.f, fmaxf(ylo - cy, cy - (ylo + inv)));
+      const float rx2 = Re * Re - dz * dz - dy * dy;
+      if (rx2 >= 0.f) {
+        const float rx = sqrtf(rx2) + 1e-4f;
+        const int x0 = max((int)floorf((cx - rx) * g.cpmx) - g.cm[0], 0), x1 = min((int)floorf((cx + rx) * g.cpmx) - g.cm[0], g.cnx - 1);
+        if (x0 <= x1) {
+          const int row = (iz * g.cny + iy) * g.cnx;
+          s = __ldg(g.cell_start + row + x0);
+          e = __ldg(g.cell_start + row + x1 + 1);
+        }
+      }
+    }
     uint32_t incl = e - s;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-      if ((int)lane >= o) incl += t;
+    for (int o = 1; o < G; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(full, incl, o, G);
+      if (gl >= o) incl += t;
     }
-    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-    for (uint32_t j0 = 0; j0 < total; j0 += 32) {
-      const uint32_t j = j0 + lane;
-      int lo = 0;
+    const uint32_t total = __shfl_sync(full, incl, G - 1, G);
+    if (!__any_sync(full, total != 0u)) continue;
+    for (uint32_t j0 = 0; __any_sync(full, j0 < total); j0 += 2 * G) {  // two steps per iteration: both loads in flight together
+      uint32_t idx[2];
 #pragma unroll
-      for (int step = 16; step; step >>= 1) {
-        const uint32_t v = __shfl_sync(0xffffffffu, incl, lo + step - 1);
-        if (v <= j) lo += step;
+      for (int u = 0; u < 2; ++u) {
+        const uint32_t j = j0 + (uint32_t)(u * G + gl);
+        int lo = 0;  // owner row = first lane of the group whose inclusive sum exceeds j
+#pragma unroll
+        for (int step = G / 2; step; step >>= 1) {
+          const uint32_t v = __shfl_sync(full, incl, lo + step - 1, G);
+          if (v <= j) lo += step;
+        }
+        lo = min(lo, G - 1);
+        const uint32_t o_incl = __shfl_sync(full, incl, lo, G);
+        const uint32_t o_e = __shfl_sync(full, e, lo, G);
+        idx[u] = j < total ? o_e - (o_incl - j) : 0xFFFFFFFFu;
       }
-      lo = min(lo, 31);
-      const uint32_t o_incl = __shfl_sync(0xffffffffu, incl, lo);
-      const uint32_t o_e = __shfl_sync(0xffffffffu, e, lo);
-      if (j < total) {
-        const float4 P = __ldg(g.pts + (o_e - (o_incl - j)));
-        const float dx = P.x - cx, dyy = P.y - cy, dzz = P.z - cz;
-        best = fminf(best, fmaf(dx, dx, fmaf(dyy, dyy, dzz * dzz)));
-      }
+      float4 P[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+        if (idx[u] != 0xFFFFFFFFu) P[u] = __ldg(g.pts + idx[u]);
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+        if (idx[u] != 0xFFFFFFFFu) {
+          const float dx = P[u].x - cx, dyy = P[u].y - cy, dzz = P[u].z - cz;
+          best = fminf(best, fmaf(dx, dx, fmaf(dyy, dyy, dzz * dzz)));
+        }
     }
+#pragma unroll
+    for (int o = G / 2; o; o >>= 1) best = fminf(best, __shfl_xor_sync(full, best, o, G));
+    Re = sqrtf(best) * 1.000001f + 1e-4f;  // never below the distance of the best point found so far
   }
 #pragma unroll
-  for (int o = 16; o; o >>= 1) best = fminf(best, __shfl_xor_sync(0xffffffffu, best, o));
+  for (int o = G / 2; o; o >>= 1) best = fminf(best, __shfl_xor_sync(full, best, o, G));
   return best;
 }
 

@@ -128,6 +128,18 @@ int tg_fk_frames(const float* q10, int64_t B, float* frames, void* stream);
  * min(exact clearance, clearance_cap) (cap = 0.25 m).                            */
 int tg_check_configs(tg_env* env, const float* arm, const float* base, int64_t B,
                      uint8_t* valid, float* clearance, void* stream);
+/* tg_check_configs for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same verdicts as
+ * tg_check_configs (no clearance output); the queue between its two kernels lives in a static device array of the library
+ * (4 MiB + 256 B, held by every GPU that loads the library until exit) instead of the handle's cudaMalloc'ed queue, and the
+ * call makes no cudaMalloc / cudaFree or other allocating call.  B <= TG_NOALLOC_MAX_CONFIGS, else TG_E_CAPACITY with a
+ * message in tg_last_error.  All calls on one device share the array: calls that overlap on the GPU (different streams or
+ * handles) race; calls on one stream are fine.  The first call per device looks the array's address up
+ * (cudaGetSymbolAddress): make it outside a stream capture.                                                             */
+#define TG_NOALLOC_QUEUE_ITEMS 65536   /* 64-byte items of the static queue; overflow is resolved inline, never wrong */
+#define TG_NOALLOC_MAX_CONFIGS 262144  /* configurations per call                                                     */
+int tg_check_configs_noalloc(tg_env* env, const float* arm, const float* base, int64_t B,
+                             uint8_t* valid, void* stream);
 /* Motion-edge validation at fixed resolution (VAMP validate_motion, used inside
  * planner_func / simplify, planning/fetch/algorithms.py:37,51): edge e runs from
  * (arm0,base0)[e] to (arm1,base1)[e]; n = max(ceil(|delta| * resolution / rake),1)

@@ -16,6 +16,8 @@ TG_N_SPHERES = 111
 TG_N_LINKS = 15
 TG_MAX_OBSTACLES = 64
 TG_MAX_ATTACHED = 64
+TG_NOALLOC_MAX_CONFIGS = 262144  # configurations per tg_check_configs_noalloc call (static scratch)
+TG_E_CAPACITY = -3
 
 _lib = None
 
@@ -49,6 +51,7 @@ _SIGS = {
     "tg_fk_spheres": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "tg_fk_frames": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "tg_check_configs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "tg_check_configs_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "tg_check_edges": (
         C.c_int,
         [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p,

@@ -14,6 +14,8 @@
 
 #include <vector>
 
+#include <mutex>
+
 #include "query.cuh"
 
 #define TG_BLOCK 128
@@ -1264,6 +1266,78 @@ int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int6
 extern "C" int tg_check_configs(tg_env* env, const float* arm, const float* base, int64_t B, uint8_t* valid, float* clearance,
                                 void* stream_) {
   return tg_check_configs_slot(env, arm, base, B, valid, clearance, stream_, -1);
+}
+
+// ---- tg_check_configs_noalloc: the configuration check with its ambiguous queue in a static device array ----------------
+// For callers that must not allocate (CUDA graph capture, tight serving loops): the queue of phase 1 -> phase 2 lives in a
+// file-scope __device__ array instead of the cudaMalloc'ed queue of the handle, and the call makes no cudaMalloc / cudaFree
+// (nor any allocating library call): two launches, one 8-byte cudaMemsetAsync.  Every GPU that loads the library holds the
+// array (4 MiB + 256 B) until exit.  All calls on a device share it: it keeps the last call's items, only the two counters
+// must start at zero (cleared on the caller's stream before phase 1); calls that overlap on the GPU (different streams or
+// handles on the same device) race on it.
+static __device__ __align__(256) unsigned char tg_noalloc_scratch[256 + (size_t)TG_NOALLOC_QUEUE_ITEMS * sizeof(TgItem)];
+
+// In host code `tg_noalloc_scratch` is a host-side stand-in, not a device address: the address the kernels get comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.
+#define TG_NOALLOC_MAX_DEVICES 64
+static void* tg_noalloc_ptr[TG_NOALLOC_MAX_DEVICES];
+static std::mutex tg_noalloc_mutex;
+static int tg_noalloc_setup(int device, unsigned char** out) {
+  TG_CHECK_ARG(device >= 0 && device < TG_NOALLOC_MAX_DEVICES, "tg_check_configs_noalloc: device index out of range");
+  std::lock_guard<std::mutex> lock(tg_noalloc_mutex);
+  if (tg_noalloc_ptr[device] == nullptr) {
+    void* p = nullptr;
+    TG_CUDA(cudaSetDevice(device));
+    TG_CUDA(cudaGetSymbolAddress(&p, tg_noalloc_scratch));
+    if (p == nullptr) {
+      tg_set_error("tg_check_configs_noalloc: cudaGetSymbolAddress returned NULL on device %d", device);
+      return TG_E_CUDA;
+    }
+    tg_noalloc_ptr[device] = p;
+  }
+  *out = (unsigned char*)tg_noalloc_ptr[device];
+  return TG_OK;
+}
+
+extern "C" int tg_check_configs_noalloc(tg_env* env, const float* arm, const float* base, int64_t B, uint8_t* valid, void* stream_) {
+  TG_CHECK_ARG(env != nullptr, "tg_check_configs_noalloc: env is NULL");
+  TG_CHECK_ARG(B >= 0 && (B == 0 || (arm && base && valid)), "tg_check_configs_noalloc: NULL buffer");
+  if (B > (int64_t)TG_NOALLOC_MAX_CONFIGS) {
+    tg_set_error("tg_check_configs_noalloc: %lld configurations exceed the maximum of %d per call (static scratch); split the batch or use tg_check_configs",
+                 (long long)B, TG_NOALLOC_MAX_CONFIGS);
+    return TG_E_CAPACITY;
+  }
+  TG_CHECK_ARG(((uintptr_t)arm & 15) == 0, "tg_check_configs_noalloc: arm must be 16-byte aligned");
+  if (B == 0) return TG_OK;
+  cudaStream_t st = (cudaStream_t)stream_;
+  TG_CUDA(cudaSetDevice(env->device));
+  unsigned char* scratch = nullptr;
+  {
+    const int rc = tg_noalloc_setup(env->device, &scratch);  // first call per device: the symbol lookup; afterwards a table read
+    if (rc) return rc;
+  }
+  const TgExtras* ex = tg_extras_ptr(env);
+  const int nb = (int)B;
+  if (env->grid.empty && ex == nullptr) {
+    k_fill_u8<<<tg_div_up(nb, 256), 256, 0, st>>>(valid, nb, 1);
+  } else {
+    const unsigned cap = env->queue_limit && env->queue_limit < (unsigned)TG_NOALLOC_QUEUE_ITEMS ? env->queue_limit : (unsigned)TG_NOALLOC_QUEUE_ITEMS;
+    TgQueue qu{reinterpret_cast<TgItem*>(scratch + 256), reinterpret_cast<unsigned*>(scratch), cap};
+    TG_CUDA(cudaMemsetAsync(qu.count, 0, 2 * sizeof(unsigned), st));
+    if (nb >= TGC_COARSE_MIN_BATCH && !env->grid.empty && !env->no_coarse) {
+      const size_t smem = sizeof(TgRing<TGC_BLOCK_COARSE>) + (((size_t)env->grid.gnx * env->grid.gny * env->grid.gnz + 15) & ~(size_t)15);
+      k_check_configs<TGC_BLOCK_COARSE, true><<<min(tg_div_up(nb, TGC_BLOCK_COARSE), env->sm_count), TGC_BLOCK_COARSE, smem, st>>>(
+          env->grid, env->thr, ex, arm, base, nb, valid, qu, env->counters_dev);
+    } else {
+      const int blocks1 = min(tg_div_up(nb, TGC_BLOCK_PLAIN), env->sm_count * env->occ_configs);
+      k_check_configs<TGC_BLOCK_PLAIN, false><<<blocks1, TGC_BLOCK_PLAIN, sizeof(TgRing<TGC_BLOCK_PLAIN>), st>>>(
+          env->grid, env->thr, ex, arm, base, nb, valid, qu, env->counters_dev);
+    }
+    if (!env->grid.empty) k_resolve<<<env->sm_count * env->occ_resolve, TGR_BLOCK, 0, st>>>(env->grid, qu, valid, env->counters_dev);
+  }
+  if (env->flags & TG_FLAG_SELF) k_self_configs<<<tg_div_up(nb, TG_BLOCK), TG_BLOCK, 0, st>>>(arm, nb, valid);
+  TG_CUDA(cudaGetLastError());
+  return TG_OK;
 }
 
 int tg_check_edges_slot(tg_env* env, const float* arm0, const float* base0, const float* arm1, const float* base1, int64_t E,

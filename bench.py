@@ -296,8 +296,7 @@ def main():
         dist.broadcast(view, 0)                   # NCCL: rank 0's blob -> every rank's own blob storage
         if rank != 0:
             w.adopt_blob(blob_bytes)              # rebase pointers, refresh the texture copy of the distance grid
-        handles = []
-        for off in range(0, n, LAUNCH_CONFIGS):   # one launch pair per chunk; its gather overlaps the next pair's kernels
+        for off in range(0, n, LAUNCH_CONFIGS):   # one launch pair per chunk, then the gather of its verdict bits
             m = min(LAUNCH_CONFIGS, n - off)
             w.check_configs_into(arm_t[off:off + m], base_t[off:off + m], valid_t[off:off + m])
             o8, m8 = off // 8, (m + 7) // 8
@@ -305,8 +304,6 @@ def main():
             # 4 MiB per rank and launch pair: 35 us alone.  Not overlapped with the next pair's kernels on purpose: an NCCL kernel
             # that shares the SMs with the persistent, whole-SM blocks of phase 1 stretched phase 1 by 0.4 ms (r02u)
             dist.all_gather_into_tensor(gathered[world * o8: world * (o8 + m8)], packed[o8:o8 + m8])
-        for h in handles:
-            h.wait()
 
     def timed(fn, steps):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -54,7 +54,7 @@ __device__ __forceinline__ void tg_push_item(const TgGrid& g, TgQueue qu, TgCoun
 // phase 1: configurations.  Persistent blocks; one lane = one configuration in both stages.
 // Stage A (20 base-pose spheres) refutes ~70 % of random configurations; the survivors are
 // compacted through a shared-memory ring so that stage B (91 spheres + the arm chain) always runs
-// with full warps.  Two block barriers per tile of TGC_BLOCK configurations.
+// with full warps.  Two (sub-)block barriers per tile of TGC_SUB configurations.
 // ------------------------------------------------------------------------------------------------
 // Two instantiations: <1024, true> - ONE block of 32 warps per SM that first copies the coarse far-field grid
 // (<= 176 KB) into shared memory, so that most spheres of a free configuration are proven free by an LDS instead of an
@@ -99,15 +99,33 @@ __device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& t
   tg_push_item(g, qu, ctr, need, idx, cl.amb, cfg, valid);
 }
 
+// A block is split into BLOCK / TGC_SUB SUB-BLOCKS of TGC_SUB threads, each with its own ring, its own tiles and its own
+// named barrier (bar.sync id, TGC_SUB): the sub-blocks share the shared-memory coarse grid but never wait for each other,
+// so the tail of one sub-block's stage B (a few warps still walking all 91 arm spheres while the others have exited
+// early) overlaps with the other sub-blocks' work instead of idling the SM at a block-wide barrier.  Phase 1 per 32 Mi
+// configurations with sub-blocks of 1024 (= one block-wide ring) / 512 / 256 / 128 threads: 1.990 / 1.893 / 1.975 / 2.027 ms
+// (profiles/r03a_sub_ab.txt; smaller sub-blocks pay more ring traffic and barriers per configuration).
+#ifndef TGC_SUB
+#define TGC_SUB 512
+#endif
+__device__ __forceinline__ void tgc_sub_barrier(int sub, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(sub + 1), "r"(nthreads) : "memory");
+}
+
 template <int BLOCK, bool COARSE>
 __global__ void __launch_bounds__(BLOCK, 1024 / BLOCK)
 k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm,
                 const float* __restrict__ base, int B, uint8_t* __restrict__ valid, TgQueue qu, TgCounters* ctr) {
-  constexpr unsigned RING = 2 * BLOCK;  // power of two
+  constexpr int SUB = TGC_SUB < BLOCK ? TGC_SUB : BLOCK;
+  constexpr int NSUB = BLOCK / SUB;
+  static_assert(BLOCK % SUB == 0 && NSUB <= 8, "sub-blocks use named barriers 1..NSUB");
+  constexpr unsigned RING = 2 * SUB;  // power of two
   extern __shared__ __align__(16) unsigned char tgc_smem[];
-  TgRing<BLOCK>& ring = *reinterpret_cast<TgRing<BLOCK>*>(tgc_smem);
-  __shared__ unsigned s_tail;
-  if (threadIdx.x == 0) s_tail = 0;
+  const int sub = threadIdx.x / SUB, tid = threadIdx.x - sub * SUB;  // warp-uniform
+  TgRing<SUB>& ring = reinterpret_cast<TgRing<SUB>*>(tgc_smem)[sub];  // NSUB rings = sizeof(TgRing<BLOCK>) bytes
+  __shared__ unsigned s_tails[8];
+  unsigned& s_tail = s_tails[sub];
+  if (tid == 0) s_tail = 0;
   TgCoarse cg;
   if constexpr (COARSE) {
     uint8_t* cgs = tgc_smem + sizeof(TgRing<BLOCK>);
@@ -124,14 +142,14 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
   __syncthreads();
   unsigned head = 0;  // ring positions count up; slot = position & (RING - 1)
   const unsigned lane = threadIdx.x & 31;
-  const int ntiles = (B + BLOCK - 1) / BLOCK;
+  const int ntiles = (B + SUB - 1) / SUB;
   // The loop body holds the only copy of stage A and stage B (the kernel is instruction-cache
   // sensitive): the last, extra iteration (tile >= ntiles) only drains what is left in the ring.
-  for (int tile = blockIdx.x;; tile += gridDim.x) {
-    const bool last = tile >= ntiles;  // block-uniform
+  for (int tile = blockIdx.x * NSUB + sub;; tile += gridDim.x * NSUB) {
+    const bool last = tile >= ntiles;  // sub-block-uniform
     float cfg[11];
     if (!last) {
-      const int i = tile * BLOCK + threadIdx.x;
+      const int i = tile * SUB + tid;
       const bool live = i < B;
       TgClass cl;
       tg_class_clear(cl);
@@ -164,13 +182,13 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
         }
       }
     }
-    __syncthreads();
-    const unsigned avail = s_tail - head;  // block-uniform: s_tail is stable between the two barriers; < 2 * BLOCK
-    const bool run_b = avail >= BLOCK || (last && avail != 0u);
-    const bool live_b = run_b && threadIdx.x < avail;
+    tgc_sub_barrier(sub, SUB);
+    const unsigned avail = *(volatile unsigned*)&s_tail - head;  // sub-block-uniform: s_tail is stable between the two barriers; < 2 * SUB
+    const bool run_b = avail >= (unsigned)SUB || (last && avail != 0u);
+    const bool live_b = run_b && (unsigned)tid < avail;
     uint32_t e_idx = 0, e_amb = 0;
-    if (run_b) {  // block-uniform
-      const unsigned sl = (head + threadIdx.x) & (RING - 1);
+    if (run_b) {  // sub-block-uniform
+      const unsigned sl = (head + (unsigned)tid) & (RING - 1);
 #pragma unroll
       for (int k = 0; k < 11; ++k) cfg[k] = 0.f;
       if (live_b) {
@@ -184,10 +202,10 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
         cfg[7] = a1.x; cfg[8] = a1.y; cfg[9] = a1.z; cfg[10] = a1.w;
       }
     }
-    __syncthreads();
+    tgc_sub_barrier(sub, SUB);
     if (run_b) {
       tg_stage_b_entry<COARSE>(g, thr, cg, ex, cfg, e_idx, e_amb, valid, qu, ctr, live_b);
-      head += min(avail, (unsigned)BLOCK);
+      head += min(avail, (unsigned)SUB);
     }
     if (last) break;
   }

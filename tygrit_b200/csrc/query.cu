@@ -145,6 +145,13 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
   const int ntiles = (B + SUB - 1) / SUB;
   // The loop body holds the only copy of stage A and stage B (the kernel is instruction-cache
   // sensitive): the last, extra iteration (tile >= ntiles) only drains what is left in the ring.
+#ifdef TGC_PREFETCH_BASE
+  float pf0 = 0.f, pf1 = 0.f, pf2 = 0.f;  // base pose of this thread's configuration in the NEXT tile, in flight during this one
+  {
+    const long long i0 = (long long)(blockIdx.x * NSUB + sub) * SUB + tid;
+    if (i0 < B) { pf0 = __ldcs(base + 3 * i0); pf1 = __ldcs(base + 3 * i0 + 1); pf2 = __ldcs(base + 3 * i0 + 2); }
+  }
+#endif
   for (int tile = blockIdx.x * NSUB + sub;; tile += gridDim.x * NSUB) {
     const bool last = tile >= ntiles;  // sub-block-uniform
     float cfg[11];
@@ -153,8 +160,17 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
       const bool live = i < B;
       TgClass cl;
       tg_class_clear(cl);
+#ifdef TGC_PREFETCH_BASE
+      cfg[0] = pf0; cfg[1] = pf1; cfg[2] = pf2;
+      {
+        const long long in = (long long)(tile + gridDim.x * NSUB) * SUB + tid;
+        if (in < B) { pf0 = __ldcs(base + 3 * in); pf1 = __ldcs(base + 3 * in + 1); pf2 = __ldcs(base + 3 * in + 2); }
+      }
+#endif
       if (live) {
+#ifndef TGC_PREFETCH_BASE
         cfg[0] = __ldcs(base + 3 * (size_t)i); cfg[1] = __ldcs(base + 3 * (size_t)i + 1); cfg[2] = __ldcs(base + 3 * (size_t)i + 2);
+#endif
         if (!g.empty) {
           const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
 #ifndef TG_LATE_COMPACT
@@ -220,14 +236,15 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
 // skipped.  Items whose sphere count exceeds the list are handled in further passes.
 // ------------------------------------------------------------------------------------------------
 #ifndef TGR_BLOCK
-#define TGR_BLOCK 96    // threads per block (64 / 96 / 128 threads: 1.417 / 1.408 / 1.462 ms per 32 Mi configurations)
+#define TGR_BLOCK 128   // threads per block.  Round 1, 72 voxels/m: 64 / 96 / 128 threads 1.417 / 1.408 / 1.462 ms per 32 Mi configurations;
+                        // round 2, 90 voxels/m (profiles/r03c_resolve_tune.txt): 64 x 16 / 96 x 10 / 96 x 12 / 128 x 8 blocks per SM 0.994 / 0.819 / 0.806 / 0.795 ms
 #endif
 #define TGR_ITEMS (TGR_BLOCK / 2)  // queue items per batch (two threads per item): small batches keep the serial sphere chain per warp short
 #ifndef TGR_CAP
 #define TGR_CAP 768     // sphere-list slots per pass
 #endif
 #ifndef TGR_MINB
-#define TGR_MINB 10
+#define TGR_MINB 8
 #endif
 #define TGR_ROUNDS 1    // best-first rounds before the rest of the list is walked in order
 
@@ -856,6 +873,9 @@ __device__ __forceinline__ void tgc_interval(const TgGrid& g, const TgMid& m, un
   }
 }
 
+// (Tightening a fine code's interval by the centre's measured offset inside its voxel, as the narrow phase does for its
+// candidates - 4 mm of 19 per side at 90 voxels/m - was measured: 2.68e8 against 2.79e8 configurations/s, the extra
+// arithmetic of the code pass costs more than the few searches it saves.)
 // clearance (optional output of tg_check_configs): exact, clipped at TG_CLEARANCE_CAP.
 // Lane-per-configuration form (used when obstacle / attachment spheres are set; the block-cooperative kernel below is the
 // default).  Pass 1 reads, for every sphere, the fine distance code (the half-resolution code where the fine one is
@@ -924,9 +944,9 @@ k_clearance(const TgGrid g, const TgMid m, const TgExtras* __restrict__ ex, cons
   clearance[i] = best;
 }
 
-// clearance, block-cooperative (the default when there are no obstacle / attachment spheres): 64 configurations per block
+// clearance, block-cooperative (the default when there are no obstacle / attachment spheres): TGCL_CFGS configurations per block
 // iteration.
-//  (1) the first 64 threads run the FK, one lane per configuration, and leave the 15 WORLD link frames in shared memory;
+//  (1) the first TGCL_CFGS threads run the FK, one lane per configuration, and leave the 15 WORLD link frames in shared memory;
 //  (2) all threads take (configuration, sphere) pairs: centre from the frame, fine distance code - where that is
 //      saturated (centre farther than ~0.3 m) the code of the half-resolution grid (TgMid, out to ~0.7 m) - kept as 10 bits
 //      per pair; a code is an interval [lo, hi] around the sphere's own clearance, the smallest hi per configuration
@@ -940,10 +960,14 @@ k_clearance(const TgGrid g, const TgMid m, const TgExtras* __restrict__ ex, cons
 // the cloud had no upper bound and searched out to 0.52 m: 80 % of the time of the first version (r02t: 5.1e7 /s).
 // Measured (r02x, 4 Mi configurations of the bench batch): lane kernel + half-resolution grid 1.60e8 /s; this kernel with
 // groups of 4 / 8 / 16 / 32 lanes at 256 threads 1.45 / 1.75 / 1.88 / 1.73e8; 512 threads, groups of 8 / 16: 2.42 / 2.65e8 /s;
-// 1024 threads, groups of 8: 1.76e8 (profiles/r02x_clearance.txt).
-#define TGCL_CFGS 64
+// 1024 threads, groups of 8: 1.76e8 (profiles/r02x_clearance.txt).  Blocks of 512 / 256 / 128 / 64 threads with 64 / 32 / 16 / 8
+// configurations per iteration (the same 1024 threads per SM, finer barriers): 2.65 / 2.79 / 2.77 / 2.67e8
+// (profiles/r03d_clearance_blocks.txt).
+#ifndef TGCL_CFGS
+#define TGCL_CFGS 32
+#endif
 #ifndef TGCL_BLOCK
-#define TGCL_BLOCK 512
+#define TGCL_BLOCK 256
 #endif
 #ifndef TGCL_G
 #define TGCL_G 16  // lanes per nearest-point search

@@ -190,6 +190,28 @@ def test_obstacles_and_attachment(tabletop):
     w.close()
 
 
+def test_clearance_with_obstacles_attachment_and_self_term(tabletop):
+    """The clearance output when obstacle / attachment spheres are set (the lane-per-configuration kernel serves these worlds)
+    and with the self-collision term: within 3e-6 m of min(cloud + extras clearance, self clearance, 0.25) in fp64."""
+    cloud, _, _ = tabletop
+    w = CollisionWorld(max_points=1 << 17)
+    w.build(cloud)
+    arm, base = synth.random_configs(3000, seed=21, base_box=(-1.2, 1.2, -1.2, 1.2))
+    obs = np.array([[0.6, 0.3, 1.0, 0.12], [0.2, -0.5, 0.5, 0.2], [-0.9, 0.9, 0.3, 0.05]], np.float32)
+    att = {"spheres": np.array([[0.1, 0.0, 0.0, 0.04], [0.18, 0.02, 0.0, 0.03]]), "pos": (0.02, 0.0, 0.01),
+           "quat": (0.0, 0.3826834, 0.0, 0.9238795)}
+    w.set_obstacles(obs)
+    w.set_attachment(att["spheres"], att["pos"], att["quat"])
+    cl = collide.CloudOracle(cloud, obstacles=obs).config_clearance(arm, base, attachment=att)
+    for self_on in (False, True):
+        w.set_self_collision(self_on)
+        ref = np.minimum(cl, cchecker.self_clearance(arm)) if self_on else cl
+        v, c = w.check_configs(_cuda(arm), _cuda(base), clearance=True)
+        _assert_verdicts(v.cpu().numpy(), ref, f"extras, self={self_on}")
+        np.testing.assert_allclose(c.cpu().numpy(), np.minimum(ref, 0.25), atol=3e-6, rtol=0)
+    w.close()
+
+
 def test_point_radius_and_coarse_grid(tabletop):
     cloud, _, cc = tabletop
     arm, base = synth.random_configs(4000, seed=13, base_box=(-1, 1, -1, 1))

@@ -23,6 +23,8 @@ p.add_argument("--touch", default="", help="comma list of NCCL uses before timin
 p.add_argument("--tag", default="")
 p.add_argument("--device", type=int, default=-1)
 p.add_argument("--steps", type=int, default=10)
+p.add_argument("--vpm", type=float, default=72.0)
+p.add_argument("--workload", default="uniform", choices=["uniform", "free"])
 a = p.parse_args()
 rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
 if a.device >= 0:
@@ -41,10 +43,12 @@ if a.mode != "none" and world > 1:
         torch.cuda.synchronize()
         if a.mode == "nccl-destroyed":
             dist.destroy_process_group()
-w = CollisionWorld(device=local, max_points=1 << 20, voxels_per_metre=72.0, max_voxels=192 << 20)
+w = CollisionWorld(device=local, max_points=1 << 20, voxels_per_metre=a.vpm, max_voxels=192 << 20)
 w.build(torch.from_numpy(synth.room_cloud(500_000)).to(dev))
 B = 64 << 20
 arm, base = synth.device_configs(B, seed=42 + rank, device=dev)
+if a.workload == "free":
+    arm, base, _ = synth.free_base_configs(w, B, seed=42 + rank, device=dev)
 valid = torch.empty(B, dtype=torch.uint8, device=dev)
 for _ in range(3):
     w.check_configs_into(arm, base, valid)

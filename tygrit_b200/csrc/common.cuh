@@ -23,7 +23,8 @@
 #define TG_FLAG_SELF 1  // tg_env.flags: self-collision term on (tg_env_set_self_collision)
 #define TG_HOST_MAX_CHUNKS 4096
 #ifndef TG_COARSE_MAX
-#define TG_COARSE_MAX 180224  // bytes of the coarse far-field grid: it lives in SHARED memory of the phase-1 kernel (176 KB)
+#define TG_COARSE_MAX 114688  // bytes of the coarse far-field grid: it lives in SHARED memory of the phase-1 kernel next to the 80 KB
+                              // ring; 112 + 80 KB keep the SM's shared-memory carve-out at 196 KB (228 KB would leave 28 KB of L1: phase 1 + 11 %)
 #endif
 #define TG_HOST_SMALL 16384  // host batches up to this size go through one packed H2D copy and one D2H copy
 

@@ -66,11 +66,18 @@ __device__ __forceinline__ void tg_push_item(const TgGrid& g, TgQueue qu, TgCoun
 #define TGC_COARSE_MIN_BATCH (1 << 18)  // configurations per launch from which the coarse variant is used
 #endif
 
+#ifndef TGC_RING_MULT
+#define TGC_RING_MULT 4
+#endif
+// ring entries per thread: up to 3 tiles of stage-A1 survivors on top of a leftover of < 1 tile
+#ifndef TGC_ILP
+#define TGC_ILP 3        // configurations per lane in one stage-A1 step (<= TGC_RING_MULT - 1)
+#endif
 template <int BLOCK>
-struct TgRing {  // survivors of stage A: base pose, index, ambiguous stage-A spheres (the arm is read by stage B)
-  float bx[2 * BLOCK], by[2 * BLOCK], bth[2 * BLOCK];
-  uint32_t idx[2 * BLOCK];
-  uint32_t amb0[2 * BLOCK];
+struct TgRing {  // survivors of stage A1: base pose, index, ambiguous stage-A spheres (the arm is read by stage B)
+  float bx[TGC_RING_MULT * BLOCK], by[TGC_RING_MULT * BLOCK], bth[TGC_RING_MULT * BLOCK];
+  uint32_t idx[TGC_RING_MULT * BLOCK];
+  uint32_t amb0[TGC_RING_MULT * BLOCK];
 };
 
 template <bool COARSE>
@@ -119,7 +126,9 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
   constexpr int SUB = TGC_SUB < BLOCK ? TGC_SUB : BLOCK;
   constexpr int NSUB = BLOCK / SUB;
   static_assert(BLOCK % SUB == 0 && NSUB <= 8, "sub-blocks use named barriers 1..NSUB");
-  constexpr unsigned RING = 2 * SUB;  // power of two
+  constexpr unsigned RING = TGC_RING_MULT * SUB;  // power of two
+  constexpr int U = TGC_ILP;
+  static_assert(U >= 1 && U < TGC_RING_MULT, "a stage-A1 step must fit the ring on top of a leftover of less than one tile");
   extern __shared__ __align__(16) unsigned char tgc_smem[];
   const int sub = threadIdx.x / SUB, tid = threadIdx.x - sub * SUB;  // warp-uniform
   TgRing<SUB>& ring = reinterpret_cast<TgRing<SUB>*>(tgc_smem)[sub];  // NSUB rings = sizeof(TgRing<BLOCK>) bytes
@@ -140,67 +149,88 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
     cg = tg_coarse_init(g, nullptr);
   }
   __syncthreads();
-  unsigned head = 0;  // ring positions count up; slot = position & (RING - 1)
+  unsigned head = 0, tail_seen = 0;  // ring positions count up; slot = position & (RING - 1)
   const unsigned lane = threadIdx.x & 31;
-  const int ntiles = (B + SUB - 1) / SUB;
-  // The loop body holds the only copy of stage A and stage B (the kernel is instruction-cache
-  // sensitive): the last, extra iteration (tile >= ntiles) only drains what is left in the ring.
-#ifdef TGC_PREFETCH_BASE
-  float pf0 = 0.f, pf1 = 0.f, pf2 = 0.f;  // base pose of this thread's configuration in the NEXT tile, in flight during this one
-  {
-    const long long i0 = (long long)(blockIdx.x * NSUB + sub) * SUB + tid;
-    if (i0 < B) { pf0 = __ldcs(base + 3 * i0); pf1 = __ldcs(base + 3 * i0 + 1); pf2 = __ldcs(base + 3 * i0 + 2); }
-  }
-#endif
-  for (int tile = blockIdx.x * NSUB + sub;; tile += gridDim.x * NSUB) {
-    const bool last = tile >= ntiles;  // sub-block-uniform
+  const long long ntiles = ((long long)B + SUB - 1) / SUB;
+  const long long stride = (long long)gridDim.x * NSUB;  // this sub-block's tiles: first, first + stride, ...
+  long long tile = (long long)blockIdx.x * NSUB + sub;
+  // One loop iteration = a stage-A1 step over up to U tiles (as many as the ring has room for), then at most one stage-B
+  // run over SUB compacted survivors.  The loop body holds the only copy of stage A and stage B (the kernel is
+  // instruction-cache sensitive); iterations without tiles left only drain the ring.
+  for (;;) {
+    const bool more = tile < ntiles;                                   // sub-block-uniform
+    // all U tiles or none: a step with fewer tiles would still execute the instructions of all U slots.  While less than one
+    // tile of survivors is waiting (stage B cannot run) the ring has room for RING / SUB - 1 >= U tiles, so there is progress.
+    const int nsub = (more && (int)((RING - (tail_seen - head)) / SUB) >= U) ? U : 0;
     float cfg[11];
-    if (!last) {
-      const int i = tile * SUB + tid;
-      const bool live = i < B;
-      TgClass cl;
-      tg_class_clear(cl);
-#ifdef TGC_PREFETCH_BASE
-      cfg[0] = pf0; cfg[1] = pf1; cfg[2] = pf2;
-      {
-        const long long in = (long long)(tile + gridDim.x * NSUB) * SUB + tid;
-        if (in < B) { pf0 = __ldcs(base + 3 * in); pf1 = __ldcs(base + 3 * in + 1); pf2 = __ldcs(base + 3 * in + 2); }
+    if (nsub > 0) {
+      // Stage A1 for U configurations per lane at once.  Alone, this stage is a chain of three dependent memory latencies
+      // (base pose, the probe of the largest sphere, the probes of the other two) that every warp of a sub-block walks in
+      // step between two barriers: with one configuration per lane it took 0.90 of phase 1's 1.89 ms per 32 Mi
+      // configurations (profiles/r03h_stage_breakdown.jsonl).  U configurations per lane share each latency.
+      long long ci[U];
+      bool live[U];
+      float b0[U], b1[U], b2[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        ci[u] = (tile + u * stride) * SUB + tid;
+        live[u] = u < nsub && ci[u] < (long long)B;
+        b0[u] = b1[u] = b2[u] = 0.f;
+        if (live[u]) {
+          b0[u] = __ldcs(base + 3 * ci[u]); b1[u] = __ldcs(base + 3 * ci[u] + 1); b2[u] = __ldcs(base + 3 * ci[u] + 2);
+        }
       }
-#endif
-      if (live) {
-#ifndef TGC_PREFETCH_BASE
-        cfg[0] = __ldcs(base + 3 * (size_t)i); cfg[1] = __ldcs(base + 3 * (size_t)i + 1); cfg[2] = __ldcs(base + 3 * (size_t)i + 2);
-#endif
-        if (!g.empty) {
-          const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
-#ifndef TG_LATE_COMPACT
-          tg_stage_a1<COARSE>(g, thr, cg, p, cl);  // compaction right after the three big spheres (the kernel is issue-bound
-                                                   // now: the other 17 ran with ~30 % of the lanes active)
+      TgClass cl[U];
+      TgPose p[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        tg_class_clear(cl[u]);
+        p[u] = tg_pose(g, b0[u], b1[u], b2[u]);
+      }
+      if (!g.empty) {
+        // the largest base sphere alone refutes 55 % of the bench's configurations, the three big ones 65 %
+#ifdef TGC_A1_BRANCHY
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (live[u]) tg_stage_a1<COARSE>(g, thr, cg, p[u], cl[u]);
 #else
-          tg_stage_a<COARSE>(g, thr, cg, p, cl);
+#pragma unroll
+        for (int u = 0; u < U; ++u) tg_group_yaw_en<0, 1, COARSE>(g, thr, cg, p[u], live[u], cl[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u) tg_group_yaw_en<1, 3, COARSE>(g, thr, cg, p[u], live[u] && !cl[u].collide, cl[u]);
 #endif
-        }
-        if (cl.collide) valid[i] = 0;
       }
-      const bool surv = live && !cl.collide;
-      const unsigned m = __ballot_sync(0xffffffffu, surv);
-      const unsigned ncol = __popc(__ballot_sync(0xffffffffu, live)) - __popc(m);
+      unsigned m[U], total = 0, ncol = 0;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (live[u] && cl[u].collide) valid[ci[u]] = 0;
+        m[u] = __ballot_sync(0xffffffffu, live[u] && !cl[u].collide);
+        ncol += __popc(__ballot_sync(0xffffffffu, live[u])) - __popc(m[u]);
+        total += __popc(m[u]);
+      }
       if (lane == 0 && ncol) atomicAdd(&ctr->definite_collisions, (unsigned long long)ncol);
-      if (m) {
+      if (total) {  // survivors keep their input order within a tile (compaction by ballot), one shared atomic per warp and step
         unsigned pos = 0;
-        if (lane == 0) pos = atomicAdd(&s_tail, (unsigned)__popc(m));
-        pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
-        if (surv) {
-          const unsigned sl = pos & (RING - 1);
-          ring.bx[sl] = cfg[0]; ring.by[sl] = cfg[1]; ring.bth[sl] = cfg[2];
-          ring.idx[sl] = (uint32_t)i;
-          ring.amb0[sl] = cl.amb[0];
+        if (lane == 0) pos = atomicAdd(&s_tail, total);
+        pos = __shfl_sync(0xffffffffu, pos, 0);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (live[u] && !cl[u].collide) {
+            const unsigned sl = (pos + __popc(m[u] & ((1u << lane) - 1u))) & (RING - 1);
+            ring.bx[sl] = b0[u]; ring.by[sl] = b1[u]; ring.bth[sl] = b2[u];
+            ring.idx[sl] = (uint32_t)ci[u];
+            ring.amb0[sl] = cl[u].amb[0];
+          }
+          pos += __popc(m[u]);
         }
       }
+      tile += (long long)nsub * stride;
     }
     tgc_sub_barrier(sub, SUB);
-    const unsigned avail = *(volatile unsigned*)&s_tail - head;  // sub-block-uniform: s_tail is stable between the two barriers; < 2 * SUB
-    const bool run_b = avail >= (unsigned)SUB || (last && avail != 0u);
+    tail_seen = *(volatile unsigned*)&s_tail;  // stable until the next stage-A1 step of this sub-block
+    const unsigned avail = tail_seen - head;   // sub-block-uniform, < RING
+    const bool drain = tile >= ntiles;         // no tiles left: run stage B on whatever remains
+    const bool run_b = avail >= (unsigned)SUB || (drain && avail != 0u);
     const bool live_b = run_b && (unsigned)tid < avail;
     uint32_t e_idx = 0, e_amb = 0;
     if (run_b) {  // sub-block-uniform
@@ -218,12 +248,12 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
         cfg[7] = a1.x; cfg[8] = a1.y; cfg[9] = a1.z; cfg[10] = a1.w;
       }
     }
-    tgc_sub_barrier(sub, SUB);
+    tgc_sub_barrier(sub, SUB);  // the popped slots may be overwritten by the next stage-A1 step from here on
     if (run_b) {
       tg_stage_b_entry<COARSE>(g, thr, cg, ex, cfg, e_idx, e_amb, valid, qu, ctr, live_b);
       head += min(avail, (unsigned)SUB);
     }
-    if (last) break;
+    if (drain && avail <= (unsigned)SUB) break;  // nothing left to read, nothing left in the ring
   }
 }
 

@@ -185,6 +185,26 @@ __device__ __forceinline__ void tg_group_yaw(const TgGrid& g, const TgThr& thr, 
   for (int k = K0; k < K1; ++k) TG_CLASSIFY_ONE(k, code[k - K0]);
 }
 
+// The same for a lane that may be switched off (`en` = false: no look-up, no probe, nothing classified).  Branch-free, so
+// that the calls for several configurations of one thread (stage A1 of the configuration kernel runs TGC_ILP of them per
+// lane) are one basic block and their probes are in flight together.
+template <int K0, int K1, bool C>
+__device__ __forceinline__ void tg_group_yaw_en(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, bool en, TgClass& out) {
+  int code[K1 - K0];
+#pragma unroll
+  for (int k = K0; k < K1; ++k) {
+    const float4 l = TGM_K_SPH[k];
+    const float gx = fmaf(p.cs, l.x, fmaf(-p.sn, l.y, p.gx0));
+    const float gy = fmaf(p.sn, l.x, fmaf(p.cs, l.y, p.gy0));
+    const float gz = g.vpm * l.z;
+    bool need = en;
+    if constexpr (C) need = need && tg_coarse_code(cg, gx, gy, gz) < thr.cfree_ge[k];
+    code[k - K0] = tg_probe_if(g, need, gx, gy, gz, TG_CODE_SKIPPED);  // a skipped sphere reads "free, not ambiguous"
+  }
+#pragma unroll
+  for (int k = K0; k < K1; ++k) TG_CLASSIFY_ONE(k, code[k - K0]);
+}
+
 // voxel-space affine map of an arm frame F (base_link frame) under base pose p
 struct TgVox {
   float G[9], gt[3];

@@ -8,7 +8,7 @@ d=json.load(open(sys.argv[1])); r=d["roofline"]
 print("%-22s value %.4g ms/step %.3f p1 %.4f p2 %.4f mism %d" % (sys.argv[2], d["value"], d["ms_per_step"], r["phase1_avg_launch_ms"], r["phase2_avg_launch_ms"], d["parity_sample"]["mismatches"]))
 PY
 }
-for v in "" u2 u2m8 u4m8; do
+for v in "" s256 s128 s1024; do
   L=$PWD/tygrit_b200/lib/libtygrit_b200${v:+_$v}.so
   [ -f $L ] || continue
   for wl in uniform free; do

@@ -193,6 +193,9 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
 #pragma unroll
         for (int u = 0; u < U; ++u)
           if (live[u]) tg_stage_a1<COARSE>(g, thr, cg, p[u], cl[u]);
+#elif defined(TG_A1_MERGED)  // the three probes of a configuration together (measured: see profiles/r03k_breakdown2.jsonl)
+#pragma unroll
+        for (int u = 0; u < U; ++u) tg_group_yaw_en<0, 3, COARSE>(g, thr, cg, p[u], live[u], cl[u]);
 #else
 #pragma unroll
         for (int u = 0; u < U; ++u) tg_group_yaw_en<0, 1, COARSE>(g, thr, cg, p[u], live[u], cl[u]);
@@ -204,6 +207,10 @@ k_check_configs(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         if (live[u] && cl[u].collide) valid[ci[u]] = 0;
+#ifdef TG_EXP_A1_ONLY
+        if (live[u] && !cl[u].collide) valid[ci[u]] = 1;
+        cl[u].collide = true;
+#endif
         m[u] = __ballot_sync(0xffffffffu, live[u] && !cl[u].collide);
         ncol += __popc(__ballot_sync(0xffffffffu, live[u])) - __popc(m[u]);
         total += __popc(m[u]);

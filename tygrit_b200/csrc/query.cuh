@@ -266,9 +266,13 @@ template <bool C>
 __device__ __forceinline__ void tg_stage_a2(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, TgClass& out) {
   // (enclosing-sphere probes for the torso column and the bumper arc were measured: they rarely prove anything inside
   // a 0.32 m window and cost 1 % more than they save)
+#ifndef TG_A2_SPLIT  // all 17 probes in flight together: one latency step less for a few more probes (phase 1 1.81 -> 1.77 ms; -DTG_A2_SPLIT: the two groups with a lane-level exit between them)
+  tg_group_yaw<3, 20, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
+#else
   tg_group_yaw<3, 9, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
   if (out.collide) return;
   tg_group_yaw<9, 20, false, C>(g, thr, cg, p, p.gx0, p.gy0, 0.f, out);
+#endif
 }
 template <bool C>
 __device__ __forceinline__ void tg_stage_a(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, TgClass& out) {

@@ -658,9 +658,17 @@ __global__ void __launch_bounds__(TGR_BLOCK, TGR_MINB) k_resolve(const TgGrid g,
 // (arm-only planning, plan_arm_rrtc) stage A is the same for every sample: it is evaluated once,
 // with the 20 base-pose spheres spread over the lanes (one probe instruction for the whole edge).
 // ------------------------------------------------------------------------------------------------
-// 72 registers, 7 blocks of 4 warps per SM.  Capping at 64 / 51 registers (8 / 10 blocks) does not pay: C2 0.689 / 0.698 ms
-// against 0.665, C5 5.55 / 5.60 against 5.58 ms/step (profiles/r02w_edge_regs_ab.txt).
-__global__ void __launch_bounds__(TG_BLOCK)
+// 64 registers, 8 blocks of 4 warps per SM, with the edge's start point and direction (22 values) parked in shared memory
+// during the rounds (TG_EDGE_SMEM_AD): C2 0.647 -> 0.623 ms, C5 5.50 -> 5.10 ms/step.  With those 22 values in registers the
+// kernel takes 72 (7 blocks), and capping it at 64 / 51 does not pay (profiles/r02w_edge_regs_ab.txt); 10 blocks (51
+// registers) do not pay here either (0.689 ms, profiles/r03l_edge_votes.txt).
+#ifndef TG_EDGE_MINB
+#define TG_EDGE_MINB 8
+#endif
+#ifndef TG_EDGE_REGS_AD
+#define TG_EDGE_SMEM_AD 1
+#endif
+__global__ void __launch_bounds__(TG_BLOCK, TG_EDGE_MINB)
 k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, const float* __restrict__ arm0,
               const float* __restrict__ base0, const float* __restrict__ arm1, const float* __restrict__ base1, int E, int rake,
               float resolution, uint8_t* __restrict__ valid, unsigned long long* __restrict__ n_checks, TgQueue qu,
@@ -714,18 +722,68 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
       const uint32_t m4[4] = {amb0_shared, 0u, 0u, 0u};
       tg_push_item(g, qu, ctr, lane == 0 && amb0_shared != 0u && !hit, (uint32_t)e, m4, a, valid);
     }
+#ifdef TG_EDGE_SMEM_AD  // start point and direction of the edge live in shared memory during the rounds (22 registers less)
+    __shared__ float s_ad[TG_BLOCK / 32][24];
+    float* sa = s_ad[threadIdx.x >> 5];
+    if (lane == 0) {
+#pragma unroll
+      for (int c = 0; c < 11; ++c) { sa[c] = a[c]; sa[12 + c] = d[c]; }
+    }
+    __syncwarp();
+#define TG_EDGE_CFG(c) fmaf(t, sa[12 + (c)], sa[(c)])
+#else
+#define TG_EDGE_CFG(c) fmaf(t, d[(c)], a[(c)])
+#endif
     for (int j = 0; j < rounds && !hit; ++j) {
       const int k = (int)lane * rounds + j + 1;
       const bool live = k <= total;
       float cfg[11];
       const float t = (float)k * inv_total;
 #pragma unroll
-      for (int c = 0; c < 11; ++c) cfg[c] = fmaf(t, d[c], a[c]);
+      for (int c = 0; c < 11; ++c) cfg[c] = TG_EDGE_CFG(c);
       TgClass cl;
       tg_class_clear(cl);
+#if !defined(TG_EDGE_ROLLED) && defined(TG_EDGE_STAGE_VOTES)
+      // MEASURED VARIANT (-DTG_EDGE_STAGE_VOTES), not the default: one colliding sample refutes the edge, so the warp votes
+      // after each stage instead of once per round - two random edges in three have a sample refuted by the three big base
+      // spheres in their first round and would skip the other 108 spheres of the lanes that were free there.  It does not
+      // pay: C2 0.634 against 0.623 ms, C5 5.21 against 5.10 ms/step at the same 64 registers (the votes cost registers:
+      // 96 without a cap; profiles/r03l_edge_votes.txt) - the kernel is bound by the latency chains of the edges that
+      // survive, not by the instructions of the ones that die.
+      const bool act = live && !g.empty;
+      const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
+      if (act && !fixed_base) tg_stage_a1<false>(g, thr, cg0, p, cl);
+      hit = __any_sync(0xffffffffu, cl.collide);
+#ifndef TG_EDGE_ONE_VOTE
+      if (!hit) {
+        if (act && !fixed_base) tg_stage_a2<false>(g, thr, cg0, p, cl);
+        hit = __any_sync(0xffffffffu, cl.collide);
+      }
+      if (!hit) {
+        if (act) tg_stage_b<false, false>(g, thr, cg0, p, cfg + 3, cl);  // derived bounds cost the edge kernel 8 %
+#else
+      if (!hit) {
+        if (act) {
+          if (!fixed_base) tg_stage_a2<false>(g, thr, cg0, p, cl);
+          if (!cl.collide) tg_stage_b<false, false>(g, thr, cg0, p, cfg + 3, cl);
+        }
+#endif
+        if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
+        hit = __any_sync(0xffffffffu, live && cl.collide);
+      }
+#else
+#ifdef TG_EDGE_NESTED_VOTES
+      const unsigned lm = __ballot_sync(0xffffffffu, live && !g.empty);
+#endif
       if (live && !g.empty) {
         const TgPose p = tg_pose(g, cfg[0], cfg[1], cfg[2]);
-#ifndef TG_EDGE_ROLLED
+#ifdef TG_EDGE_NESTED_VOTES
+        if (!fixed_base) tg_stage_a1<false>(g, thr, cg0, p, cl);
+        if (!__any_sync(lm, cl.collide)) {
+          if (!fixed_base) tg_stage_a2<false>(g, thr, cg0, p, cl);
+          if (!__any_sync(lm, cl.collide)) tg_stage_b<false, false>(g, thr, cg0, p, cfg + 3, cl);
+        }
+#elif !defined(TG_EDGE_ROLLED)
         if (!fixed_base) tg_stage_a<false>(g, thr, cg0, p, cl);
         if (!cl.collide) tg_stage_b<false, false>(g, thr, cg0, p, cfg + 3, cl);  // derived bounds cost the edge kernel 8 %
 #else  // loops over constant tables instead of the unrolled probes: 18 % less code, but C2 0.66 -> 0.79 ms (r02j): not the default
@@ -735,6 +793,7 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
       }
       if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
       hit = __any_sync(0xffffffffu, live && cl.collide);
+#endif
       if (!hit) {
         const bool need = live && (cl.amb[0] | cl.amb[1] | cl.amb[2] | cl.amb[3]) != 0u;
         tg_push_item(g, qu, ctr, need, (uint32_t)e, cl.amb, cfg, valid);

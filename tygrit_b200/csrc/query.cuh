@@ -291,6 +291,81 @@ __device__ __forceinline__ int tg_bound_code_arm(const TgGrid& g, const TgThr& t
   return tg_probe(g, gx, gy, gz);
 }
 
+// The arm chain in two passes (-DTG_ARM_TWO_PASS).  The chain as written in tg_stage_b is up to 14 dependent probe
+// latencies (per link: the enclosing-sphere probe, then the members if it did not prove them free).  Here pass 1 runs the
+// FK chain once and issues the seven enclosing-sphere probes without looking at them (they are in flight together), and
+// pass 2 - only for lanes with at least one group to look into - runs the chain again up to the last such link and probes
+// the members there.  Same probes, same classification; the second FK pass costs ~400 instructions per warp that needs it.
+// MEASURED VARIANT, not the default: parity-green and 20 % SLOWER (phase 1 1.777 -> 2.138 ms per 32 Mi configurations, free-heavy
+// batch 4.25 -> 4.92 ms, C2 0.622 -> 0.667 ms; profiles/r03n_arm_two_pass.txt).  Unlike stage A1, stage B is not waiting for its
+// probes: what it lacks is issue slots, and the second FK pass takes more of them.
+#define TG_ARM_CHILD(dst, src, NAME, kind, qi) \
+  tg_frame_child(src, TGM_OFF_##NAME##_X, TGM_OFF_##NAME##_Y, TGM_OFF_##NAME##_Z, kind, q[qi], dst)
+template <bool DERIVE, bool C>
+__device__ __forceinline__ void tg_arm_two_pass(const TgGrid& g, const TgThr& thr, const TgCoarse& cg, const TgPose& p, const float* q,
+                                                float tz, TgClass& out) {
+  TgFrame T, F, H;
+  TgVox V;
+  tg_frame_identity(T);
+  T.t[0] = TGM_OFF_TORSO_X;
+  T.t[2] = tz;
+  int bc1, bc2, bc3, bc4, bc5, bc6, bc7;
+  TG_ARM_CHILD(F, T, SHOULDER_PAN, 4, 1);  tg_vox_frame(g, p, F, V); bc1 = tg_bound_code_arm<3, C>(g, thr, cg, V);
+  TG_ARM_CHILD(H, F, SHOULDER_LIFT, 3, 2); tg_vox_frame(g, p, H, V); bc2 = tg_bound_code_arm<4, C>(g, thr, cg, V);
+  TG_ARM_CHILD(F, H, UPPERARM_ROLL, 2, 3); tg_vox_frame(g, p, F, V); bc3 = tg_bound_code_arm<5, C>(g, thr, cg, V);
+  TG_ARM_CHILD(H, F, ELBOW_FLEX, 3, 4);    tg_vox_frame(g, p, H, V); bc4 = tg_bound_code_arm<6, C>(g, thr, cg, V);
+  TG_ARM_CHILD(F, H, FOREARM_ROLL, 2, 5);  tg_vox_frame(g, p, F, V); bc5 = tg_bound_code_arm<7, C>(g, thr, cg, V);
+  TG_ARM_CHILD(H, F, WRIST_FLEX, 3, 6);    tg_vox_frame(g, p, H, V); bc6 = tg_bound_code_arm<8, C>(g, thr, cg, V);
+  TG_ARM_CHILD(F, H, WRIST_ROLL, 2, 7);    tg_vox_frame(g, p, F, V); bc7 = tg_bound_code_arm<9, C>(g, thr, cg, V);
+  unsigned need = (bc1 < thr.bound_ge[3] ? 1u : 0u) | (bc2 < thr.bound_ge[4] ? 2u : 0u) | (bc3 < thr.bound_ge[5] ? 4u : 0u) |
+                  (bc4 < thr.bound_ge[6] ? 8u : 0u) | (bc5 < thr.bound_ge[7] ? 16u : 0u) | (bc6 < thr.bound_ge[8] ? 32u : 0u);
+  if (bc7 < thr.bound_ge[9]) {  // the last link's frame is still here
+    tg_group_arm<93, 99, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc7, out);
+    if (out.collide) return;
+    tg_group_arm<99, 111, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc7, out);
+    if (out.collide) return;
+  }
+  if (need == 0u) return;
+  TG_ARM_CHILD(F, T, SHOULDER_PAN, 4, 1);
+  if (need & 1u) {
+    tg_vox_frame(g, p, F, V);
+    tg_group_arm<55, 59, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc1, out);
+    if (out.collide) return;
+  }
+  if ((need >> 1) == 0u) return;
+  TG_ARM_CHILD(H, F, SHOULDER_LIFT, 3, 2);
+  if (need & 2u) {
+    tg_vox_frame(g, p, H, V);
+    tg_group_arm<59, 66, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc2, out);
+    if (out.collide) return;
+  }
+  if ((need >> 2) == 0u) return;
+  TG_ARM_CHILD(F, H, UPPERARM_ROLL, 2, 3);
+  if (need & 4u) {
+    tg_vox_frame(g, p, F, V);
+    tg_group_arm<66, 74, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc3, out);
+    if (out.collide) return;
+  }
+  if ((need >> 3) == 0u) return;
+  TG_ARM_CHILD(H, F, ELBOW_FLEX, 3, 4);
+  if (need & 8u) {
+    tg_vox_frame(g, p, H, V);
+    tg_group_arm<74, 80, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc4, out);
+    if (out.collide) return;
+  }
+  if ((need >> 4) == 0u) return;
+  TG_ARM_CHILD(F, H, FOREARM_ROLL, 2, 5);
+  if (need & 16u) {
+    tg_vox_frame(g, p, F, V);
+    tg_group_arm<80, 87, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc5, out);
+    if (out.collide) return;
+  }
+  if ((need >> 5) == 0u) return;
+  TG_ARM_CHILD(H, F, WRIST_FLEX, 3, 6);
+  tg_vox_frame(g, p, H, V);
+  tg_group_arm<87, 93, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc6, out);
+}
+
 // Stage B: torso + head (35 spheres, base yaw + torso lift) and the 7-joint arm chain (56 spheres).
 // The small spheres are grouped (head, ears, one group per arm link); one probe at the centre of a
 // group's enclosing sphere that proves it free skips the whole group, which is the common case for a
@@ -318,6 +393,10 @@ __device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, co
       if (out.collide) return;
     }
   }
+#ifdef TG_ARM_TWO_PASS
+  tg_arm_two_pass<DERIVE, C>(g, thr, cg, p, q, tz, out);
+}
+#else
   TgFrame T, F, H;
   TgVox V;
   tg_frame_identity(T);
@@ -367,6 +446,7 @@ __device__ __forceinline__ void tg_stage_b(const TgGrid& g, const TgThr& thr, co
     tg_group_arm<99, 111, DERIVE, C && TG_COARSE_MEMBERS>(g, thr, cg, V, bc, out);
   }
 }
+#endif
 
 // ------------------------------------------------------------------------------------------------
 // ROLLED stage A / stage B for the edge kernel (-DTG_EDGE_ROLLED; a measured variant, NOT the default).  The unrolled

@@ -147,6 +147,26 @@ def test_ragged_and_degenerate_batches(room):
     torch.cuda.synchronize()
 
 
+def test_batch_sizes_at_the_launch_shape_boundaries(tabletop):
+    """Batch sizes on both sides of every boundary of the configuration kernel's launch shape: one sub-block tile (512), one
+    three-tile stage-A1 step (1536), the switch to the coarse-grid variant (2^18) and one full step of every sub-block of
+    every SM (3 x 512 x 2 x SM count); every configuration against the fp64 oracle, and a prefix of a large batch must get
+    the verdicts it gets alone (the ring carries survivors across steps)."""
+    cloud, w, cc = tabletop
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    full = 3 * 512 * 2 * sms
+    arm, base = synth.random_configs(full + 1537, seed=77, base_box=(-1.2, 1.2, -1.2, 1.2))
+    cl = cc.clearance(arm, base, cap=1e-3)
+    a, b = _cuda(arm), _cuda(base)
+    ref_big = w.check_configs(a, b).cpu().numpy()
+    _assert_verdicts(ref_big, cl, "largest batch")
+    for n in (1, 511, 512, 513, 1535, 1536, 1537, 3071, 3073, (1 << 18) - 1, 1 << 18, (1 << 18) + 1, full - 1, full, full + 1):
+        got = w.check_configs(a[:n], b[:n]).cpu().numpy()
+        _assert_verdicts(got, cl[:n], f"batch of {n}")
+        dec = np.abs(cl[:n]) > BAND
+        assert np.array_equal(got[dec], ref_big[:n][dec]), f"batch of {n}: verdicts differ from the same configurations in the large batch"
+
+
 def test_empty_single_and_nonfinite_clouds():
     w = CollisionWorld(max_points=4096)
     arm, base = synth.random_configs(500, seed=5)

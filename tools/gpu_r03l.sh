@@ -1,6 +1,6 @@
 #!/bin/bash
 # edge kernel: warp votes between the stages of a round (A1 | A2 | B), register caps
-for v in nov sv8 sn8 sv sv10; do
+for v in prev "" prev ""; do
   L=$PWD/tygrit_b200/lib/libtygrit_b200${v:+_$v}.so
   [ -f $L ] || continue
   echo "== ${v:-votes}"

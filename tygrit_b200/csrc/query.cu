@@ -685,15 +685,22 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
       a[3 + k] = __ldg(arm0 + 8 * (size_t)e + k);
       d[3 + k] = __ldg(arm1 + 8 * (size_t)e + k);
     }
-    double s2 = 0.0;  // |b - a|^2 in fp64, order x, y, theta, q0..q7 (matches oracle/collide.py edge_n)
+    // |b - a|^2 in fp64, order x, y, theta, q0..q7 (matches oracle/collide.py edge_n).  The values are warp-uniform and the fp64
+    // pipe is narrow: one lane does the arithmetic, the sample count is broadcast.
+    int n = 0;
+    if (lane == 0) {
+      double s2 = 0.0;
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-      const double dk = (double)d[k] - (double)a[k];
-      s2 = s2 + dk * dk;
-      d[k] = d[k] - a[k];
+      for (int k = 0; k < 11; ++k) {
+        const double dk = (double)d[k] - (double)a[k];
+        s2 = s2 + dk * dk;
+      }
+      const double nn = ceil(sqrt(s2) * ((double)resolution / (double)rake));
+      n = nn < 1.0 ? 1 : (nn > 1.0e6 ? 1000000 : (int)nn);
     }
-    const double nn = ceil(sqrt(s2) * ((double)resolution / (double)rake));
-    const int n = nn < 1.0 ? 1 : (nn > 1.0e6 ? 1000000 : (int)nn);
+    n = __shfl_sync(0xffffffffu, n, 0);
+#pragma unroll
+    for (int k = 0; k < 11; ++k) d[k] = d[k] - a[k];
     const int total = rake * n;
     const int rounds = (total + 31) >> 5;
     if (lane == 0) my_checks += (unsigned long long)total;

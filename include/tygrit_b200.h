@@ -125,7 +125,10 @@ int tg_fk_frames(const float* q10, int64_t B, float* frames, void* stream);
 /* ---- verdicts ------------------------------------------------------------------ */
 /* validate_whole_body_config for a batch (vamp_preview.py:159-163,328-338).
  * valid: DEVICE B bytes.  clearance: DEVICE B f32 or NULL; when given it receives
- * min(exact clearance, clearance_cap) (cap = 0.25 m).                            */
+ * min(exact clearance, clearance_cap) (cap = 0.25 m), within 3e-6 m of fp64.  The first
+ * call with a clearance output after a build / import also builds a half-resolution
+ * distance grid on `stream` (3 launches; its buffer is allocated on first use, so make
+ * that call outside a stream capture).                                           */
 int tg_check_configs(tg_env* env, const float* arm, const float* base, int64_t B,
                      uint8_t* valid, float* clearance, void* stream);
 /* tg_check_configs for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid

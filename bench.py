@@ -40,7 +40,7 @@ F_TEST = 9.0            # flop per executed narrow-phase point test (SURVEY.md Â
 B_CFG = 49.0            # algorithmic HBM bytes per configuration (44 in + 1 out + 4 clearance)
 CLOUD_POINTS = 500_000
 BASE_BOX = (-3.5, 3.5, -2.5, 2.5)
-LAUNCH_CONFIGS = 32 * 1024 * 1024   # configurations per launch pair of the device API (4 x the ambiguous queue)
+LAUNCH_CONFIGS = 64 * 1024 * 1024   # configurations per launch pair of the device API (8 x the ambiguous queue)
 PARITY_SAMPLE = 1 << 20
 
 

@@ -106,7 +106,7 @@ def test_room_configs_vs_c_oracle(room):
 
 
 def test_queue_overflow_resolves_inline_with_same_verdicts(room):
-    """A launch pair takes up to 32 Mi configurations against an 8 Mi-item queue; items that do not fit are resolved
+    """A launch pair takes up to 64 Mi configurations against an 8 Mi-item queue; items that do not fit are resolved
     inline by their own lane.  Shrink the queue (test hook) so that most items overflow: verdicts and edge verdicts must
     not change, and the overflow counter must say the path ran."""
     cloud, w, cc = room
@@ -397,7 +397,7 @@ def test_edge_properties(room):
 
 
 def test_full_size_chunk_independence(room):
-    """BASELINE-size batches cross the library's launch boundaries (2^17 edges, 32 Mi configurations per launch pair):
+    """BASELINE-size batches cross the library's launch boundaries (2^19 edges, 64 Mi configurations per launch pair):
     the verdict of a unit must not depend on where in the batch it sits.  Size-independent property: a permuted batch
     gives the permuted verdicts, and a slice re-checked on its own gives the same bytes."""
     cloud, w, cc = room
@@ -413,8 +413,8 @@ def test_full_size_chunk_independence(room):
     assert np.array_equal(ev_s, ev[sl])
     cl, _ = cc.edge_clearance(a0[sl], b0[sl], a1[sl], b1[sl])
     _assert_verdicts(ev_s, cl, "edges across a launch boundary")
-    # configurations: 40 Mi = two launch pairs (32 Mi + 8 Mi); generated on the device, checked by slices + the C oracle
-    B = 40 * (1 << 20)
+    # configurations: 72 Mi = two launch pairs (64 Mi + 8 Mi); generated on the device, checked by slices + the C oracle
+    B = 72 * (1 << 20)
     g = torch.Generator(device="cuda")
     g.manual_seed(63)
     lo = torch.tensor(synth.JOINT_LOWER, dtype=torch.float32, device="cuda")
@@ -425,7 +425,7 @@ def test_full_size_chunk_independence(room):
     base = torch.rand(B, 3, generator=g, device="cuda") * (bhi - blo) + blo
     valid = w.check_configs(arm, base)
     assert w.counters()["overflow_inline"] == 0
-    for start in (0, (32 << 20) - 1000, B - 2000):                     # head, the launch boundary, tail
+    for start in (0, (32 << 20) - 1000, (64 << 20) - 1000, B - 2000):  # head, middle, the launch boundary, tail
         s2 = slice(start, start + 2000)
         again = w.check_configs(arm[s2].contiguous(), base[s2].contiguous())
         assert torch.equal(again, valid[s2])

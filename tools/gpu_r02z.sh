@@ -12,7 +12,7 @@ python tools/bench_configs.py > gpurun_out/${TAG}_bench_configs.jsonl 2> gpurun_
 python tools/clearance_time.py > gpurun_out/${TAG}_clearance.jsonl 2>&1
 python tools/clearance_time.py --workload free >> gpurun_out/${TAG}_clearance.jsonl 2>&1
 EXTRA=l1tex__m_l1tex2xbar_req_cycles_active.avg.pct_of_peak_sustained_elapsed,l1tex__m_xbar2l1tex_read_sectors.sum,lts__t_sectors.sum,lts__t_requests.sum,lts__t_sectors_srcunit_tex.sum,l1tex__t_requests_pipe_tex.sum,l1tex__t_sectors_pipe_tex.sum,l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum,smsp__inst_executed_op_shared_ld.sum
-CMD="python bench.py --configs 33554432 --steps 2 --warmup 3 --no-e2e --no-cpu --no-extras"
+CMD="python bench.py --configs 67108864 --steps 2 --warmup 3 --no-e2e --no-cpu --no-extras"
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_list.log 2>&1
 $CMD > gpurun_out/${TAG}_plain2.log 2>&1 &&

@@ -1340,13 +1340,13 @@ int tg_check_configs_slot(tg_env* env, const float* arm, const float* base, int6
   const TgExtras* ex = tg_extras_ptr(env);
   TgQueue qu = tg_queue_slot(env, slot);
 #ifndef TG_CHUNK_MULT
-#define TG_CHUNK_MULT 4
+#define TG_CHUNK_MULT 8
 #endif
-  // Configurations per launch pair: 4 x the queue capacity (device API: 8 Mi items -> 32 Mi configurations).  Both
-  // kernels are persistent and pay a drain tail per launch: 2 Mi -> 32 Mi configurations per launch is +29 % throughput
-  // on the 64 Mi bench.  Only a few per cent of the configurations produce a queue item; should more than a quarter
-  // of a launch do so, the items that do not fit are resolved inline by their own lane (tg_resolve_inline) — slower,
-  // never wrong.
+  // Configurations per launch pair: 8 x the queue capacity (device API: 8 Mi items -> 64 Mi configurations).  Both
+  // kernels are persistent and pay a drain tail per launch: 2 Mi -> 32 Mi configurations per launch was +29 % throughput
+  // on the 64 Mi bench, 32 -> 64 Mi another 1.6 % (5.157 -> 5.074 ms).  Only a few per cent of the configurations produce a
+  // queue item (3 % on the bench batch, 8 % on the free-heavy one); should more than an eighth of a launch do so, the
+  // items that do not fit are resolved inline by their own lane (tg_resolve_inline) — slower, never wrong.
   const int64_t chunk = (int64_t)(slot < 0 ? env->queue_capacity : env->queue_capacity / 2) * TG_CHUNK_MULT;
   for (int64_t off = 0; off < B; off += chunk) {
     const int nb = (int)((B - off) < chunk ? (B - off) : chunk);

@@ -46,7 +46,7 @@ __device__ __forceinline__ void tg_push_item(const TgGrid& g, TgQueue qu, TgCoun
     for (int i = 0; i < 4; ++i) dst[i] = src[i];
   } else {  // queue full: resolve right here (slow, rare, still exact)
     atomicAdd(&ctr->overflow_inline, 1ull);
-    if (tg_resolve_item(g, cfg, amb)) valid[target] = 0;
+    if (tg_resolve_item_v(g, cfg, amb)) valid[target] = 0;
   }
 }
 
@@ -97,7 +97,7 @@ __device__ __forceinline__ void tg_stage_b_entry(const TgGrid& g, const TgThr& t
 #endif
       tg_stage_b<true, COARSE>(g, thr, cg, p, cfg + 3, cl);
     }
-    if (!cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
+    if (!cl.collide && ex != nullptr) cl.collide = tg_extras_hit_v(g, *ex, cfg);
     valid[idx] = cl.collide ? 0 : 1;
   }
   const unsigned ncol = __popc(__ballot_sync(0xffffffffu, live && cl.collide));
@@ -775,7 +775,7 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
           if (!cl.collide) tg_stage_b<false, false>(g, thr, cg0, p, cfg + 3, cl);
         }
 #endif
-        if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
+        if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit_v(g, *ex, cfg);
         hit = __any_sync(0xffffffffu, live && cl.collide);
       }
 #else
@@ -798,7 +798,7 @@ k_check_edges(const TgGrid g, const TgThr thr, const TgExtras* __restrict__ ex, 
         if (!cl.collide) tg_stage_b_rolled(g, thr, p, cfg + 3, cl);
 #endif
       }
-      if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
+      if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit_v(g, *ex, cfg);
       hit = __any_sync(0xffffffffu, live && cl.collide);
 #endif
       if (!hit) {
@@ -920,7 +920,7 @@ k_check_edges_sync(const TgGrid g, const TgThr thr, const TgExtras* __restrict__
         if (!fixed_base) tg_stage_a<false>(g, thr, cg0, p, cl);
         if (!cl.collide) tg_stage_b<false, false>(g, thr, cg0, p, cfg + 3, cl);
       }
-      if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit(g, *ex, cfg);
+      if (live && !cl.collide && ex != nullptr) cl.collide = tg_extras_hit_v(g, *ex, cfg);
       const bool hit = __any_sync(0xffffffffu, live && cl.collide);
       if (!hit) {
         const bool need = live && (cl.amb[0] | cl.amb[1] | cl.amb[2] | cl.amb[3]) != 0u;

@@ -986,3 +986,24 @@ static __device__ __noinline__ bool tg_resolve_item(const TgGrid& g, const float
   }
   return false;
 }
+
+// Call-by-copy fronts of the two out-of-line helpers.  A pointer argument to a __noinline__ function forces the caller's
+// array into local memory for its whole life: with the configuration (x, y, theta, q0..q7) living on the stack, every use of
+// a joint angle in stage B was a local-memory load behind the store that put it there.  Passing a copy at these (rare) call
+// sites keeps the hot copy in registers: phase 1 - 6 % (3.524 -> 3.311 ms per 64 Mi configurations, free-heavy batch
+// 8.43 -> 7.92 ms; profiles/r03q_cfg_copy.txt).
+__device__ __forceinline__ bool tg_extras_hit_v(const TgGrid& g, const TgExtras& ex, const float* cfg) {
+  float c2[11];
+#pragma unroll
+  for (int i = 0; i < 11; ++i) c2[i] = cfg[i];
+  return tg_extras_hit(g, ex, c2);
+}
+__device__ __forceinline__ bool tg_resolve_item_v(const TgGrid& g, const float* cfg, const uint32_t* mask) {
+  float c2[11];
+  uint32_t m2[4];
+#pragma unroll
+  for (int i = 0; i < 11; ++i) c2[i] = cfg[i];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) m2[i] = mask[i];
+  return tg_resolve_item(g, c2, m2);
+}

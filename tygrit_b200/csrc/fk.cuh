@@ -14,11 +14,19 @@
 // shared out-of-line slow path.  The library sincosf inlines its Payne-Hanek branch at every call
 // site; with eight joints per configuration that was a quarter of the query kernels' code and
 // showed up as instruction-cache stalls.
-static __device__ __noinline__ void tg_sincos_slow(float x, float* s, float* c) { sincosf(x, s, c); }
+// (The slow path returns by value: handing the caller's result pointers to an out-of-line function would force every sine and
+// cosine of the kernels through local memory.)
+static __device__ __noinline__ float2 tg_sincos_slow(float x) {
+  float s, c;
+  sincosf(x, &s, &c);
+  return make_float2(s, c);
+}
 
 __device__ __forceinline__ void tg_sincos(float x, float* sn, float* cs) {
   if (!(fabsf(x) < 1000.0f)) {
-    tg_sincos_slow(x, sn, cs);
+    const float2 r = tg_sincos_slow(x);
+    *sn = r.x;
+    *cs = r.y;
     return;
   }
   const float k = rintf(x * 0.636619747f);

@@ -1,6 +1,6 @@
 #!/bin/bash
 # edge kernel: warp votes between the stages of a round (A1 | A2 | B), register caps
-for v in prev "" prev ""; do
+for v in "" e7 e6; do
   L=$PWD/tygrit_b200/lib/libtygrit_b200${v:+_$v}.so
   [ -f $L ] || continue
   echo "== ${v:-votes}"

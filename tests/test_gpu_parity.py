@@ -285,6 +285,24 @@ def test_host_api_matches_device_api_and_chunks(room):
     assert np.array_equal(dev, again)                                  # deterministic
 
 
+def test_host_clearances_right_after_a_build_across_pipeline_chunks():
+    """The half-resolution grid of the clearance query is built lazily by the FIRST clearance call after a build; the host
+    pipeline alternates between two streams, so the second chunk must not read it before the first chunk's stream has
+    finished building it.  Fresh world, 2.3 M configurations (three chunks), clearances vs the device path and the oracle."""
+    cloud = synth.room_cloud(150_000, seed=5)
+    w = CollisionWorld(max_points=1 << 18, voxels_per_metre=64.0)
+    w.build(_cuda(cloud))
+    arm, base = synth.random_configs(2_300_000, seed=23)
+    hv, hc = w.check_configs_host(arm, base, clearance=True)           # first clearance call on this structure
+    dv, dc = w.check_configs(_cuda(arm), _cuda(base), clearance=True)
+    assert np.array_equal(hv, dv.cpu().numpy())
+    assert np.array_equal(hc, dc.cpu().numpy())
+    sub = np.concatenate([np.arange(1_040_000, 1_060_000), np.arange(2_090_000, 2_110_000)])   # around the chunk boundaries
+    ref = cchecker.CCloud(cloud).clearance(arm[sub], base[sub], cap=0.25)
+    np.testing.assert_allclose(hc[sub], ref, atol=3e-6, rtol=0)
+    w.close()
+
+
 def _read_structure(w):
     """Read the distance grid and the coarse far-field grid back from the structure blob (tg_env_grid_info gives the layout)."""
     gi = w.grid_info()

@@ -1087,6 +1087,9 @@ int tg_env_ensure_mid(tg_env* env, cudaStream_t st) {
   k_mid_bits<<<dim3(nwx, tg_div_up(gm.ny, 8), gm.nz), dim3(32, 8), 0, st>>>(g.df, g.nx, g.ny, g.nz, bits, gm.nx, gm.ny, nwx);
   tg_launch_edt<32>(bits, (uint32_t*)env->g2, env->mid, 0, gm, nxp, nwx, st);
   TG_CUDA(cudaGetLastError());
+  // once per structure: the grid must be complete before ANY stream of this handle reads it (the host pipeline alternates
+  // between two streams) and before a later build reuses the scratch buffers
+  TG_CUDA(cudaStreamSynchronize(st));
   env->launches += 3;
   env->midg.mg = env->mid;
   env->midg.nx = gm.nx; env->midg.ny = gm.ny; env->midg.nz = gm.nz;

@@ -482,9 +482,11 @@ def main():
         probes_s = executed["probes_per_config"] * cfg_per_launch / (k1_ms * 1e-3)
         req_peak = sms * pk["sm_max_mhz"] * 1e6
         roofline["binding_resource"] = {
-            "name": "L1-miss request rate of phase 1 (one 32-byte sector request per SM per clock; every probe of a lane is its own sector)",
+            "name": "phase 1: stage A is bound by dependent probe latencies, stage B by instruction issue (ncu: smsp__issue_active 77 %, "
+                    "18.6 of 32 lanes active; DESIGN.md 5.2 / 8); the L1-miss request rate (one 32-byte sector request per SM per clock, every "
+                    "probe of a lane its own sector) that bound round 1's kernel at 0.65 is the fraction reported here",
             "achieved_probes_per_s": probes_s, "peak_requests_per_s": req_peak, "frac": probes_s / req_peak,
-            "counter": "l1tex__m_l1tex2xbar_req_cycles_active (profiles/r02*_ncu_full_summary.txt)",
+            "counter": "l1tex__m_l1tex2xbar_req_cycles_active 46 %, smsp__issue_active (profiles/r06z_ncu_full_summary.txt)",
         }
         # executed work: 18 flop sphere transform + 20 flop probe per executed probe, 401 flop of arm-chain frames for the
         # configurations that reach stage B, 9 flop per narrow-phase point test

@@ -52,10 +52,10 @@ def parse():
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--configs", type=int, default=64 * 1024 * 1024, help="configurations per GPU per step (weak) = total of the strong run")
     p.add_argument("--cpu-sample", type=int, default=8_000_000, help="configurations per CPU-baseline sample")
-    p.add_argument("--vpm", type=float, default=90.0,
-                   help="distance-grid voxels per metre: the cloud of C4 is static, and since phase 1 takes most of its proofs from the coarse "
-                        "shared-memory grid its time no longer depends on the fine grid's size, while the narrow phase shrinks with the voxel "
-                        "(sweep 64/72/80/90/100 in profiles/r02g_vpm_sweep.txt); the library default stays 50")
+    p.add_argument("--vpm", type=float, default=100.0,
+                   help="distance-grid voxels per metre (the library's maximum): the cloud of C4 is static, and since phase 1 takes most of its "
+                        "proofs from the coarse shared-memory grid its time no longer depends on the fine grid's size, while the narrow phase "
+                        "shrinks with the voxel (sweeps in profiles/r02g_vpm_sweep.txt and r03s_vpm_sweep.txt); the library default stays 50")
     p.add_argument("--cpm", type=float, default=0.0, help="narrow-phase cells per metre (0 = library default)")
     p.add_argument("--cpmx", type=float, default=0.0, help="narrow-phase cells per metre along x (with --cpm = y/z; 0 = same as --cpm)")
     p.add_argument("--workload", default="uniform", choices=["uniform", "free"],

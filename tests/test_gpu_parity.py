@@ -603,14 +603,14 @@ def test_synth_depth_kernel_matches_numpy_twin():
 # ------------------------------------------------------------------ the benchmarked configuration itself
 @pytest.fixture(scope="module")
 def bench_world():
-    """What bench.py times: the 500k-point room cloud with the distance grid at 90 voxels/m (bench.py's --vpm default)."""
+    """What bench.py times: the 500k-point room cloud with the distance grid at 100 voxels/m (bench.py's --vpm default)."""
     cloud = synth.room_cloud(500_000)
-    w = CollisionWorld(max_points=1 << 20, voxels_per_metre=90.0, max_voxels=192 << 20)
+    w = CollisionWorld(max_points=1 << 20, voxels_per_metre=100.0, max_voxels=192 << 20)
     w.build(_cuda(cloud))
     return cloud, w, cchecker.CCloud(cloud)
 
 
-def test_bench_configuration_500k_90vpm_vs_fp64_oracle(bench_world):
+def test_bench_configuration_500k_100vpm_vs_fp64_oracle(bench_world):
     cloud, w, cc = bench_world
     dev = torch.device("cuda", 0)
     arm, base = synth.device_configs(300_000, seed=42, device=dev)       # bench.py's own generator and seed

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Verdict + exact clearance on the bench cloud (500k-point room, 90 voxels/m): time per batch and the largest difference
+"""Verdict + exact clearance on the bench cloud (500k-point room, 100 voxels/m): time per batch and the largest difference
 from the fp64 oracle on a sample.  TYGRIT_B200_LIB selects a variant build.
 
   python tools/clearance_time.py [--configs N] [--sample M] [--workload uniform|free]
@@ -20,7 +20,7 @@ from tygrit_b200.engine import CollisionWorld  # noqa: E402
 p = argparse.ArgumentParser()
 p.add_argument("--configs", type=int, default=1 << 22)
 p.add_argument("--sample", type=int, default=1 << 17)
-p.add_argument("--vpm", type=float, default=90.0)
+p.add_argument("--vpm", type=float, default=100.0)
 p.add_argument("--workload", default="uniform", choices=["uniform", "free"])
 a = p.parse_args()
 

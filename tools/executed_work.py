@@ -24,7 +24,7 @@ from tygrit_b200.engine import CollisionWorld  # noqa: E402
 
 p = argparse.ArgumentParser()
 p.add_argument("--configs", type=int, default=1 << 22)
-p.add_argument("--vpm", type=float, default=90.0)
+p.add_argument("--vpm", type=float, default=100.0)
 p.add_argument("--points", type=int, default=500_000)
 p.add_argument("--workload", default="uniform", choices=["uniform", "free"])
 a = p.parse_args()
